@@ -1,0 +1,115 @@
+/*
+ * Thin C-ABI launcher interface between the C host side (es_gridder.c) and
+ * the sm_100a kernels (es_kernels.cu). Plain pointers and sizes only.
+ * Every function enqueues work on `stream` and returns a cudaError_t as int
+ * (0 == cudaSuccess); nothing here synchronises unless stated.
+ */
+#ifndef ES_DEVICE_H_
+#define ES_DEVICE_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ES_TILE 64 /* uv tile edge in grid cells; must be >= support + 1 */
+
+/* Geometry shared by all kernels (doubles: coordinates are always fp64). */
+typedef struct EsGeom
+{
+    int32_t num_rows, num_chan, image_size, grid_size, support;
+    int32_t num_planes;    /* global lattice size P */
+    int32_t do_wstacking;
+    int32_t is_double;     /* data precision: 0 fp32, 1 fp64 */
+    int32_t ntile;         /* tiles per axis = ceil(grid_size / ES_TILE) */
+    int32_t plane_begin;   /* owned w-plane range [plane_begin, plane_end) */
+    int32_t plane_end;
+    int32_t pad_;
+    double beta, pixel_size, uv_scale, w_scale, inv_w_scale, min_plane_w;
+    double conv_corr_norm_factor;
+} EsGeom;
+
+typedef void* es_stream_t; /* cudaStream_t */
+
+/* Bytes of one sorted visibility record for the given precision. */
+size_t es_record_bytes(int is_double);
+
+/* ---- presort (once per grid / degrid call) ---- */
+
+/* Per visibility (row, chan): number of (tile) entries it produces for the
+ * owned plane range -> counts[row * C + chan] (uint8). */
+int es_launch_count_entries(const EsGeom* g, const void* uvw, const void* freq,
+        uint8_t* counts, es_stream_t stream);
+
+/* Exclusive prefix sum uint8 counts -> uint32 offsets (n + 1 outputs: the
+ * last one is the total). temp == NULL: only *temp_bytes is set. */
+int es_scan_counts(const uint8_t* counts, uint32_t* offsets, int64_t n,
+        void* temp, size_t* temp_bytes, es_stream_t stream);
+
+/* Emit (key, value) = (tile_id * PK + first owned plane - plane_begin,
+ * visibility index) at offsets[vis] .. */
+int es_launch_emit_entries(const EsGeom* g, const void* uvw, const void* freq,
+        const uint32_t* offsets, uint64_t* keys, uint32_t* vals,
+        es_stream_t stream);
+
+/* Stable LSD radix sort of the pairs on key bits [0, end_bit).
+ * temp == NULL: only *temp_bytes is set. */
+int es_sort_entries(const uint64_t* keys_in, uint64_t* keys_out,
+        const uint32_t* vals_in, uint32_t* vals_out, int64_t num_entries,
+        int end_bit, void* temp, size_t* temp_bytes, es_stream_t stream);
+
+/* tile_start[t] = first sorted entry of tile t (t in [0, ntile^2]); */
+int es_launch_tile_bounds(const EsGeom* g, const uint64_t* keys,
+        int64_t num_entries, uint32_t* tile_start, es_stream_t stream);
+
+/* Build the sorted records. vis/weight non-NULL: scatter records carrying the
+ * weighted (conjugated if w < 0) visibility; NULL: gather records carrying
+ * the flip sign. */
+int es_launch_build_records(const EsGeom* g, const void* uvw, const void* freq,
+        const void* vis, const void* weight, const uint64_t* keys,
+        const uint32_t* vals, int64_t num_entries, void* records,
+        es_stream_t stream);
+
+/* ---- per batch of resident w-planes [first_plane, first_plane + nplanes) ---- */
+
+/* Gridding: write every cell of the nplanes planes (zero where empty). */
+int es_launch_scatter(const EsGeom* g, const void* records,
+        const uint64_t* keys, const uint32_t* tile_start, int first_plane,
+        int nplanes, void* planes, es_stream_t stream);
+
+/* dirty += sum_planes Re(plane_centre * w-screen) (after the inverse FFT). */
+int es_launch_apply_screen(const EsGeom* g, const void* planes,
+        int first_plane, int nplanes, void* dirty, es_stream_t stream);
+
+/* planes = zero-padded(dirty * conj w-screen) (before the forward FFT). */
+int es_launch_reverse_screen(const EsGeom* g, const void* dirty,
+        int first_plane, int nplanes, void* planes, es_stream_t stream);
+
+/* Degridding: acc[entry] += sum_cells plane * kernel for the batch. */
+int es_launch_gather(const EsGeom* g, const void* records,
+        const uint64_t* keys, const uint32_t* tile_start, int first_plane,
+        int nplanes, const void* planes, void* acc, es_stream_t stream);
+
+/* vis[index] += acc[entry] (imag * flip) over all entries. */
+int es_launch_finish_degrid(const EsGeom* g, const void* records,
+        const void* acc, int64_t num_entries, void* vis, es_stream_t stream);
+
+/* ---- once per call ---- */
+
+/* dirty *= 1 / (C(l) C(m) C(n) C(0)^2); tables are device doubles. */
+int es_launch_correct(const EsGeom* g, void* dirty, const double* quad_kernel,
+        const double* quad_nodes, const double* quad_weights,
+        const double* conv_corr, es_stream_t stream);
+
+/* hist[p] += number of visibilities whose first w-plane is p (int64[P] device,
+ * pre-zeroed). */
+int es_launch_plane_histogram(const EsGeom* g, const void* uvw,
+        const void* freq, unsigned long long* hist, es_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif

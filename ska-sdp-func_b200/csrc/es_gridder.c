@@ -1,0 +1,1025 @@
+/*
+ * sdp_GridderUvwEsFft for B200: C host side (plan object, argument contract,
+ * staging, w-plane batch loop, cuFFT) over the thin C-ABI kernel launchers of
+ * es_device.h. Replaces the reference's
+ *   src/ska-sdp-func/grid_data/sdp_gridder_uvw_es_fft.cpp
+ * behind the same four entry points.
+ *
+ * Schedule per call (reference: es_fft.cpp:578-698 / :832-952, one plane at a
+ * time, every visibility re-scanned per plane, memset + atomics):
+ *   presort once  -> for each BATCH of B resident w-planes:
+ *     grid:   scatter (writes every cell once) -> batched cuFFT inverse ->
+ *             w-screen multiply + accumulate into the image (one RMW per batch)
+ *     degrid: reverse w-screen (writes every cell once) -> batched cuFFT
+ *             forward -> gather into per-record accumulators
+ *   -> grid correction / un-permute.
+ * There is no CPU fallback: without a CUDA device plan creation fails with
+ * SDP_ERR_MEM_ALLOC_FAILURE exactly like the reference does (es_fft.cpp:491-518).
+ */
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <cuda_runtime_api.h>
+#include <cufft.h>
+
+#include "es_device.h"
+#include "es_plan.h"
+#include "ska-sdp-func/grid_data/sdp_gridder_uvw_es_fft_b200.h"
+
+#define ES_MAX_PLANE_BATCH 8
+#define ES_NUM_FFT_PLANS 2
+
+typedef struct EsBuffer
+{
+    void* ptr;
+    size_t bytes;
+} EsBuffer;
+
+struct sdp_GridderUvwEsFft
+{
+    sdp_EsPlanInfo info;
+    EsGeom geom;
+    double pixsize_x_rad, pixsize_y_rad;
+    cudaStream_t stream;
+
+    /* multi-GPU extension */
+    int32_t plane_begin, plane_end, apply_correction;
+
+    /* device tables (always double) */
+    double* d_quad_kernel;
+    double* d_quad_nodes;
+    double* d_quad_weights;
+    double* d_conv_corr;
+
+    /* resident w-planes and FFT */
+    int32_t plane_batch;
+    EsBuffer planes;
+    cufftHandle fft[ES_NUM_FFT_PLANS];
+    int32_t fft_batch[ES_NUM_FFT_PLANS];
+    EsBuffer fft_work;
+
+    /* presort work space (grow-only) */
+    EsBuffer counts, offsets, keys_a, keys_b, vals_a, vals_b, records;
+    EsBuffer tile_start, sort_temp, acc;
+
+    /* staging for host arrays */
+    EsBuffer st_uvw, st_freq, st_vis, st_weight, st_dirty;
+
+    sdp_EsCallStats stats;
+    int32_t timing;
+    cudaEvent_t ev[8];
+    int32_t have_events;
+};
+
+/* ------------------------------------------------------------ utilities */
+
+static int cuda_failed(cudaError_t err, const char* what, sdp_Error* status)
+{
+    if (err == cudaSuccess) return 0;
+    if (!*status) *status = SDP_ERR_RUNTIME;
+    SDP_LOG_ERROR("%s failed: %s", what, cudaGetErrorString(err));
+    (void) cudaGetLastError();
+    return 1;
+}
+
+#define ES_CUDA(call) \
+    do { if (cuda_failed((cudaError_t) (call), #call, status)) return; } while (0)
+
+static void buffer_free(EsBuffer* b)
+{
+    if (b->ptr) (void) cudaFree(b->ptr);
+    b->ptr = 0;
+    b->bytes = 0;
+}
+
+/* Grow-only device buffer. */
+static void buffer_reserve(EsBuffer* b, size_t bytes, sdp_Error* status)
+{
+    if (*status || bytes <= b->bytes) return;
+    buffer_free(b);
+    const cudaError_t err = cudaMalloc(&b->ptr, bytes);
+    if (err != cudaSuccess || !b->ptr)
+    {
+        *status = SDP_ERR_MEM_ALLOC_FAILURE;
+        SDP_LOG_CRITICAL("GPU memory allocation failure: %s "
+                "(requested %zu bytes)", cudaGetErrorString(err), bytes);
+        (void) cudaGetLastError();
+        b->ptr = 0;
+        return;
+    }
+    b->bytes = bytes;
+}
+
+static size_t real_bytes(const sdp_GridderUvwEsFft* plan)
+{
+    return plan->info.is_double ? 8 : 4;
+}
+
+/* ------------------------------------------------- argument validation */
+
+/* Same checks, same order, same codes as es_fft.cpp:72-243. */
+static void check_buffers(const sdp_Mem* uvw, const sdp_Mem* freq_hz,
+        const sdp_Mem* vis, const sdp_Mem* weight, const sdp_Mem* dirty_image,
+        int do_degridding, sdp_Error* status)
+{
+    const sdp_MemLocation where = sdp_mem_location(uvw);
+    if (where != sdp_mem_location(freq_hz) || where != sdp_mem_location(vis) ||
+            where != sdp_mem_location(weight) ||
+            where != sdp_mem_location(dirty_image))
+    {
+        *status = SDP_ERR_MEM_LOCATION;
+        SDP_LOG_ERROR("Memory location mismatch.");
+        return;
+    }
+    const struct { const sdp_Mem* mem; int want_complex; const char* msg; }
+    kinds[] = {
+        {uvw, 0, "uvw values must be real."},
+        {freq_hz, 0, "Frequency values must be real."},
+        {vis, 1, "Visibility values must be complex."},
+        {weight, 0, "Weight values must be real."},
+        {dirty_image, 0, "Dirty image must be real"}
+    };
+    for (size_t k = 0; k < sizeof(kinds) / sizeof(kinds[0]); ++k)
+    {
+        if ((sdp_mem_is_complex(kinds[k].mem) != 0) != kinds[k].want_complex)
+        {
+            *status = SDP_ERR_DATA_TYPE;
+            SDP_LOG_ERROR("%s", kinds[k].msg);
+            return;
+        }
+    }
+    const int64_t rows = sdp_mem_shape_dim(vis, 0);
+    const int64_t chans = sdp_mem_shape_dim(vis, 1);
+    if (sdp_mem_shape_dim(uvw, 0) != rows)
+    {
+        *status = SDP_ERR_INVALID_ARGUMENT;
+        SDP_LOG_ERROR("The number of rows in uvw and vis must match.");
+        SDP_LOG_ERROR("uvw is %lld by %lld, vis is %lld by %lld",
+                (long long) sdp_mem_shape_dim(uvw, 0),
+                (long long) sdp_mem_shape_dim(uvw, 1),
+                (long long) rows, (long long) chans);
+        return;
+    }
+    if (sdp_mem_shape_dim(uvw, 1) != 3)
+    {
+        *status = SDP_ERR_INVALID_ARGUMENT;
+        SDP_LOG_ERROR("uvw must be N x 3 (it is %lld by %lld).",
+                (long long) sdp_mem_shape_dim(uvw, 0),
+                (long long) sdp_mem_shape_dim(uvw, 1));
+        return;
+    }
+    if (sdp_mem_shape_dim(freq_hz, 0) != chans)
+    {
+        *status = SDP_ERR_INVALID_ARGUMENT;
+        SDP_LOG_ERROR("The number of channels in vis and freq_hz must match "
+                "(freq_hz has %lld, vis is %lld by %lld).",
+                (long long) sdp_mem_shape_dim(freq_hz, 0),
+                (long long) rows, (long long) chans);
+        return;
+    }
+    if (sdp_mem_shape_dim(weight, 0) != rows ||
+            sdp_mem_shape_dim(weight, 1) != chans)
+    {
+        *status = SDP_ERR_INVALID_ARGUMENT;
+        SDP_LOG_ERROR("weight and vis must be the same size "
+                "(weight is %lld by %lld, vis is %lld by %lld).",
+                (long long) sdp_mem_shape_dim(weight, 0),
+                (long long) sdp_mem_shape_dim(weight, 1),
+                (long long) rows, (long long) chans);
+        return;
+    }
+    if (sdp_mem_shape_dim(dirty_image, 0) != sdp_mem_shape_dim(dirty_image, 1))
+    {
+        *status = SDP_ERR_INVALID_ARGUMENT;
+        SDP_LOG_ERROR("Dirty image must be square (it is %lld by %lld).",
+                (long long) sdp_mem_shape_dim(dirty_image, 0),
+                (long long) sdp_mem_shape_dim(dirty_image, 1));
+        return;
+    }
+    const int dbl = sdp_mem_type(uvw) == SDP_MEM_DOUBLE;
+    if (!dbl && sdp_mem_type(uvw) != SDP_MEM_FLOAT)
+    {
+        *status = SDP_ERR_DATA_TYPE;
+        SDP_LOG_ERROR("uvw must be single or double precision.");
+        return;
+    }
+    const sdp_MemType want_real = dbl ? SDP_MEM_DOUBLE : SDP_MEM_FLOAT;
+    const sdp_MemType want_cplx = dbl ?
+            SDP_MEM_COMPLEX_DOUBLE : SDP_MEM_COMPLEX_FLOAT;
+    if (sdp_mem_type(freq_hz) != want_real || sdp_mem_type(vis) != want_cplx ||
+            sdp_mem_type(weight) != want_real ||
+            sdp_mem_type(dirty_image) != want_real)
+    {
+        *status = SDP_ERR_DATA_TYPE;
+        SDP_LOG_ERROR("All buffers must be the same precision.");
+        return;
+    }
+    if (!sdp_mem_is_c_contiguous(uvw) || !sdp_mem_is_c_contiguous(freq_hz) ||
+            !sdp_mem_is_c_contiguous(vis) ||
+            !sdp_mem_is_c_contiguous(weight) ||
+            !sdp_mem_is_c_contiguous(dirty_image))
+    {
+        *status = SDP_ERR_INVALID_ARGUMENT;
+        SDP_LOG_ERROR("All input arrays must be C contiguous");
+        return;
+    }
+    if (do_degridding ? sdp_mem_is_read_only(vis) :
+            sdp_mem_is_read_only(dirty_image))
+    {
+        *status = SDP_ERR_INVALID_ARGUMENT;
+        SDP_LOG_ERROR(do_degridding ? "Visibility data must be writable." :
+                "Dirty image must be writable.");
+        return;
+    }
+}
+
+/* es_fft.cpp:246-262 */
+static void check_parameters(double pixsize_x_rad, double pixsize_y_rad,
+        sdp_Error* status)
+{
+    if (pixsize_x_rad != pixsize_y_rad)
+    {
+        *status = SDP_ERR_INVALID_ARGUMENT;
+        SDP_LOG_ERROR("Only square images supported, so pixsize_x_rad and "
+                "pixsize_y_rad must be equal (%.12e vs %.12e).",
+                pixsize_x_rad, pixsize_y_rad);
+    }
+}
+
+/* Shapes are frozen at plan creation in the reference (es_fft.cpp:310-313,
+ * 560) and later calls are trusted; here a mismatch would run past the ends
+ * of the work buffers, so it is rejected. */
+static void check_against_plan(const sdp_GridderUvwEsFft* plan,
+        const sdp_Mem* vis, const sdp_Mem* dirty_image, sdp_Error* status)
+{
+    if (*status) return;
+    if (sdp_mem_shape_dim(vis, 0) != plan->info.num_rows ||
+            sdp_mem_shape_dim(vis, 1) != plan->info.num_chan ||
+            sdp_mem_shape_dim(dirty_image, 0) != plan->info.image_size ||
+            (sdp_mem_is_double(vis) != 0) != (plan->info.is_double != 0))
+    {
+        *status = SDP_ERR_INVALID_ARGUMENT;
+        SDP_LOG_ERROR("Array shapes or precision differ from those the plan "
+                "was created for.");
+    }
+}
+
+/* ---------------------------------------------------------------- plan */
+
+void sdp_gridder_uvw_es_fft_plan_info(int32_t num_rows, int32_t num_chan,
+        int32_t image_size, int32_t is_double, double pixel_size_rad,
+        double epsilon, double min_abs_w, double max_abs_w,
+        int32_t do_w_stacking, sdp_EsPlanInfo* info, double* quad_kernel,
+        double* quad_nodes, double* quad_weights, double* conv_corr,
+        sdp_Error* status)
+{
+    if (*status || !info) return;
+    es_plan_scalars(num_rows, num_chan, image_size, is_double, pixel_size_rad,
+            epsilon, min_abs_w, max_abs_w, do_w_stacking, info);
+    double qk[ES_QUADRATURE_BOUND], qn[ES_QUADRATURE_BOUND];
+    double qw[ES_QUADRATURE_BOUND];
+    info->conv_corr_norm_factor = es_correction_tables(image_size,
+            info->grid_size, info->support, info->beta, qk, qn, qw, conv_corr);
+    if (quad_kernel) memcpy(quad_kernel, qk, sizeof(qk));
+    if (quad_nodes) memcpy(quad_nodes, qn, sizeof(qn));
+    if (quad_weights) memcpy(quad_weights, qw, sizeof(qw));
+}
+
+void sdp_gridder_uvw_es_fft_get_info(const sdp_GridderUvwEsFft* plan,
+        sdp_EsPlanInfo* info)
+{
+    if (plan && info) *info = plan->info;
+}
+
+void sdp_gridder_uvw_es_fft_free_plan(sdp_GridderUvwEsFft* plan)
+{
+    if (!plan) return;
+    for (int k = 0; k < ES_NUM_FFT_PLANS; ++k)
+        if (plan->fft_batch[k] > 0) (void) cufftDestroy(plan->fft[k]);
+    if (plan->d_quad_kernel) (void) cudaFree(plan->d_quad_kernel);
+    if (plan->d_quad_nodes) (void) cudaFree(plan->d_quad_nodes);
+    if (plan->d_quad_weights) (void) cudaFree(plan->d_quad_weights);
+    if (plan->d_conv_corr) (void) cudaFree(plan->d_conv_corr);
+    EsBuffer* all[] = {
+        &plan->planes, &plan->fft_work, &plan->counts, &plan->offsets,
+        &plan->keys_a, &plan->keys_b, &plan->vals_a, &plan->vals_b,
+        &plan->records, &plan->tile_start, &plan->sort_temp, &plan->acc,
+        &plan->st_uvw, &plan->st_freq, &plan->st_vis, &plan->st_weight,
+        &plan->st_dirty
+    };
+    for (size_t k = 0; k < sizeof(all) / sizeof(all[0]); ++k)
+        buffer_free(all[k]);
+    if (plan->have_events)
+        for (int k = 0; k < 8; ++k) (void) cudaEventDestroy(plan->ev[k]);
+    free(plan);
+}
+
+static double* upload_table(const double* host, size_t count,
+        sdp_Error* status)
+{
+    if (*status) return 0;
+    double* dev = 0;
+    cudaError_t err = cudaMalloc((void**) &dev, count * sizeof(double));
+    if (err != cudaSuccess || !dev)
+    {
+        *status = SDP_ERR_MEM_ALLOC_FAILURE;
+        SDP_LOG_CRITICAL("GPU memory allocation failure: %s "
+                "(requested %zu bytes)", cudaGetErrorString(err),
+                count * sizeof(double));
+        (void) cudaGetLastError();
+        return 0;
+    }
+    err = cudaMemcpy(dev, host, count * sizeof(double),
+            cudaMemcpyHostToDevice);
+    if (err != cudaSuccess)
+    {
+        *status = SDP_ERR_MEM_COPY_FAILURE;
+        SDP_LOG_CRITICAL("cudaMemcpy error: %s", cudaGetErrorString(err));
+        (void) cudaGetLastError();
+    }
+    return dev;
+}
+
+/* How many w-planes to keep resident: as many as fit comfortably (planes +
+ * an equally large cuFFT work area), at most ES_MAX_PLANE_BATCH. */
+static int choose_plane_batch(const sdp_GridderUvwEsFft* plan)
+{
+    const char* env = getenv("SKA_SDP_FUNC_ES_PLANE_BATCH");
+    int limit = ES_MAX_PLANE_BATCH;
+    if (env && atoi(env) > 0) limit = atoi(env);
+    size_t free_b = 0, total_b = 0;
+    if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess)
+    {
+        (void) cudaGetLastError();
+        return 1;
+    }
+    const double plane_bytes = 2.0 * (double) real_bytes(plan) *
+            (double) plan->info.grid_size * (double) plan->info.grid_size;
+    int fit = (int) (0.35 * (double) free_b / (2.0 * plane_bytes));
+    if (fit < 1) fit = 1;
+    int batch = plan->info.num_total_w_grids;
+    if (batch > limit) batch = limit;
+    if (batch > fit) batch = fit;
+    return batch < 1 ? 1 : batch;
+}
+
+sdp_GridderUvwEsFft* sdp_gridder_uvw_es_fft_create_plan(
+        const sdp_Mem* uvw, const sdp_Mem* freq_hz, const sdp_Mem* vis,
+        const sdp_Mem* weight, const sdp_Mem* dirty_image,
+        const double pixel_size_x_rad, const double pixel_size_y_rad,
+        const double epsilon, const double min_abs_w, const double max_abs_w,
+        const int do_w_stacking, sdp_Error* status)
+{
+    if (*status) return 0;
+    check_parameters(pixel_size_x_rad, pixel_size_y_rad, status);
+    if (*status) return 0;
+    check_buffers(uvw, freq_hz, vis, weight, dirty_image, 0, status);
+    if (*status) return 0;
+    const int64_t rows = sdp_mem_shape_dim(vis, 0);
+    const int64_t chans = sdp_mem_shape_dim(vis, 1);
+    if (rows * chans >= 2147483647LL)
+    {
+        /* same limit as the reference's 32-bit i_vis (kernels.cu:150-152) */
+        *status = SDP_ERR_INVALID_ARGUMENT;
+        SDP_LOG_ERROR("Too many visibilities for one plan (rows x channels "
+                "must be below 2^31).");
+        return 0;
+    }
+
+    sdp_GridderUvwEsFft* plan =
+            (sdp_GridderUvwEsFft*) calloc(1, sizeof(sdp_GridderUvwEsFft));
+    if (!plan)
+    {
+        *status = SDP_ERR_MEM_ALLOC_FAILURE;
+        return 0;
+    }
+    plan->pixsize_x_rad = pixel_size_x_rad;
+    plan->pixsize_y_rad = pixel_size_y_rad;
+    const int is_double = sdp_mem_is_double(vis) ? 1 : 0;
+    const int image_size = (int) sdp_mem_shape_dim(dirty_image, 0);
+    es_plan_scalars((int) rows, (int) chans, image_size, is_double,
+            pixel_size_x_rad, epsilon, min_abs_w, max_abs_w, do_w_stacking,
+            &plan->info);
+    double qk[ES_QUADRATURE_BOUND], qn[ES_QUADRATURE_BOUND];
+    double qw[ES_QUADRATURE_BOUND];
+    double* cc = (double*) calloc((size_t) image_size / 2 + 1, sizeof(double));
+    if (!cc)
+    {
+        *status = SDP_ERR_MEM_ALLOC_FAILURE;
+        free(plan);
+        return 0;
+    }
+    plan->info.conv_corr_norm_factor = es_correction_tables(image_size,
+            plan->info.grid_size, plan->info.support, plan->info.beta,
+            qk, qn, qw, cc);
+    if (plan->info.grid_size < ES_TILE / 4 ||
+            plan->info.support + 1 > 17 || plan->info.num_total_w_grids < 1 ||
+            !(plan->info.w_scale > 0.0) || !isfinite(plan->info.w_scale))
+    {
+        *status = SDP_ERR_INVALID_ARGUMENT;
+        SDP_LOG_ERROR("Cannot build a w-plane lattice for these parameters "
+                "(grid %d, support %d, planes %d, w_scale %g).",
+                plan->info.grid_size, plan->info.support,
+                plan->info.num_total_w_grids, plan->info.w_scale);
+        free(cc);
+        free(plan);
+        return 0;
+    }
+
+    EsGeom* g = &plan->geom;
+    g->num_rows = plan->info.num_rows;
+    g->num_chan = plan->info.num_chan;
+    g->image_size = image_size;
+    g->grid_size = plan->info.grid_size;
+    g->support = plan->info.support;
+    g->num_planes = plan->info.num_total_w_grids;
+    g->do_wstacking = plan->info.do_wstacking;
+    g->is_double = is_double;
+    g->ntile = (g->grid_size + ES_TILE - 1) / ES_TILE;
+    g->beta = plan->info.beta;
+    g->pixel_size = plan->info.pixel_size;
+    g->uv_scale = plan->info.uv_scale;
+    g->w_scale = plan->info.w_scale;
+    g->inv_w_scale = plan->info.inv_w_scale;
+    g->min_plane_w = plan->info.min_plane_w;
+    g->conv_corr_norm_factor = plan->info.conv_corr_norm_factor;
+    plan->plane_begin = 0;
+    plan->plane_end = g->num_planes;
+    plan->apply_correction = 1;
+    plan->stream = 0; /* legacy default stream, like the reference */
+
+    /* Device side: tables and the resident w-planes (the reference allocates
+     * its single plane here too, es_fft.cpp:509-518). */
+    plan->d_quad_kernel = upload_table(qk, ES_QUADRATURE_BOUND, status);
+    plan->d_quad_nodes = upload_table(qn, ES_QUADRATURE_BOUND, status);
+    plan->d_quad_weights = upload_table(qw, ES_QUADRATURE_BOUND, status);
+    plan->d_conv_corr = upload_table(cc, (size_t) image_size / 2 + 1, status);
+    free(cc);
+    if (!*status)
+    {
+        plan->plane_batch = choose_plane_batch(plan);
+        const size_t plane_bytes = 2 * real_bytes(plan) *
+                (size_t) g->grid_size * (size_t) g->grid_size;
+        while (plan->plane_batch >= 1)
+        {
+            sdp_Error try_status = SDP_SUCCESS;
+            buffer_reserve(&plan->planes,
+                    plane_bytes * (size_t) plan->plane_batch, &try_status);
+            if (!try_status) break;
+            if (plan->plane_batch == 1) { *status = try_status; break; }
+            plan->plane_batch /= 2;
+        }
+    }
+    if (*status)
+    {
+        sdp_gridder_uvw_es_fft_free_plan(plan);
+        return 0;
+    }
+    plan->stats.plane_batch = plan->plane_batch;
+    return plan;
+}
+
+void sdp_gridder_uvw_es_fft_set_plane_range(sdp_GridderUvwEsFft* plan,
+        int32_t plane_begin, int32_t plane_end, int32_t apply_correction,
+        sdp_Error* status)
+{
+    if (*status || !plan) return;
+    if (plane_begin < 0 || plane_end > plan->geom.num_planes ||
+            plane_begin > plane_end)
+    {
+        *status = SDP_ERR_INVALID_ARGUMENT;
+        SDP_LOG_ERROR("Invalid w-plane range [%d, %d) for a lattice of %d "
+                "planes.", plane_begin, plane_end, plan->geom.num_planes);
+        return;
+    }
+    plan->plane_begin = plane_begin;
+    plan->plane_end = plane_end;
+    plan->apply_correction = apply_correction;
+}
+
+void sdp_gridder_uvw_es_fft_enable_timing(sdp_GridderUvwEsFft* plan,
+        int32_t enable)
+{
+    if (plan) plan->timing = enable;
+}
+
+void sdp_gridder_uvw_es_fft_get_stats(const sdp_GridderUvwEsFft* plan,
+        sdp_EsCallStats* stats)
+{
+    if (plan && stats) *stats = plan->stats;
+}
+
+/* ----------------------------------------------------------------- FFT */
+
+/* Batched in-place 2-D C2C / Z2Z plan over `batch` contiguous planes, cached;
+ * all cached plans share one work area. Same transform as the reference asks
+ * of cuFFT (sdp_fft.cpp:362-456), only batched and created once. */
+static cufftHandle* fft_plan_for(sdp_GridderUvwEsFft* plan, int batch,
+        sdp_Error* status)
+{
+    if (*status) return 0;
+    int slot = -1;
+    for (int k = 0; k < ES_NUM_FFT_PLANS; ++k)
+        if (plan->fft_batch[k] == batch) return &plan->fft[k];
+    for (int k = 0; k < ES_NUM_FFT_PLANS; ++k)
+        if (plan->fft_batch[k] == 0) { slot = k; break; }
+    if (slot < 0)
+    {
+        slot = ES_NUM_FFT_PLANS - 1;
+        (void) cufftDestroy(plan->fft[slot]);
+        plan->fft_batch[slot] = 0;
+    }
+    cufftHandle h;
+    cufftResult rc = cufftCreate(&h);
+    if (rc == CUFFT_SUCCESS) rc = cufftSetAutoAllocation(h, 0);
+    int n[2] = {plan->geom.grid_size, plan->geom.grid_size};
+    size_t work = 0;
+    if (rc == CUFFT_SUCCESS)
+        rc = cufftMakePlanMany(h, 2, n, 0, 1, 0, 0, 1, 0,
+                plan->info.is_double ? CUFFT_Z2Z : CUFFT_C2C, batch, &work);
+    if (rc != CUFFT_SUCCESS)
+    {
+        *status = SDP_ERR_RUNTIME;
+        SDP_LOG_ERROR("Error in cufftMakePlanMany (code %d)", (int) rc);
+        (void) cufftDestroy(h);
+        return 0;
+    }
+    if (work > plan->fft_work.bytes)
+    {
+        /* all plans must be re-pointed at the new area */
+        (void) cudaStreamSynchronize(plan->stream);
+        buffer_reserve(&plan->fft_work, work, status);
+        if (*status) { (void) cufftDestroy(h); return 0; }
+        for (int k = 0; k < ES_NUM_FFT_PLANS; ++k)
+            if (plan->fft_batch[k] > 0)
+                (void) cufftSetWorkArea(plan->fft[k], plan->fft_work.ptr);
+    }
+    rc = cufftSetWorkArea(h, plan->fft_work.ptr);
+    if (rc == CUFFT_SUCCESS) rc = cufftSetStream(h, plan->stream);
+    if (rc != CUFFT_SUCCESS)
+    {
+        *status = SDP_ERR_RUNTIME;
+        SDP_LOG_ERROR("Error configuring cuFFT plan (code %d)", (int) rc);
+        (void) cufftDestroy(h);
+        return 0;
+    }
+    plan->fft[slot] = h;
+    plan->fft_batch[slot] = batch;
+    return &plan->fft[slot];
+}
+
+static void fft_exec(sdp_GridderUvwEsFft* plan, int batch, int forward,
+        sdp_Error* status)
+{
+    cufftHandle* h = fft_plan_for(plan, batch, status);
+    if (*status || !h) return;
+    cufftResult rc;
+    const int dir = forward ? CUFFT_FORWARD : CUFFT_INVERSE;
+    if (plan->info.is_double)
+        rc = cufftExecZ2Z(*h, (cufftDoubleComplex*) plan->planes.ptr,
+                (cufftDoubleComplex*) plan->planes.ptr, dir);
+    else
+        rc = cufftExecC2C(*h, (cufftComplex*) plan->planes.ptr,
+                (cufftComplex*) plan->planes.ptr, dir);
+    if (rc != CUFFT_SUCCESS)
+    {
+        *status = SDP_ERR_RUNTIME;
+        SDP_LOG_ERROR("Error in cufftExec (code %d)", (int) rc);
+    }
+    plan->stats.fft_execs++;
+}
+
+/* -------------------------------------------------------------- staging */
+
+typedef struct EsArrays
+{
+    const void* uvw;
+    const void* freq;
+    void* vis;
+    const void* weight;
+    void* dirty;
+    int staged;
+} EsArrays;
+
+static size_t mem_bytes(const sdp_Mem* m)
+{
+    int64_t n = 1;
+    for (int32_t d = 0; d < sdp_mem_num_dims(m); ++d)
+        n *= sdp_mem_shape_dim(m, d);
+    return (size_t) (n * sdp_mem_type_size(sdp_mem_type(m)));
+}
+
+static void stage_in(sdp_GridderUvwEsFft* plan, EsBuffer* b,
+        const sdp_Mem* m, sdp_Error* status)
+{
+    const size_t bytes = mem_bytes(m);
+    buffer_reserve(b, bytes > 0 ? bytes : 16, status);
+    if (*status || bytes == 0) return;
+    const cudaError_t err = cudaMemcpyAsync(b->ptr, sdp_mem_data_const(m),
+            bytes, cudaMemcpyHostToDevice, plan->stream);
+    if (err != cudaSuccess)
+    {
+        *status = SDP_ERR_MEM_COPY_FAILURE;
+        SDP_LOG_CRITICAL("cudaMemcpy error: %s", cudaGetErrorString(err));
+        (void) cudaGetLastError();
+        return;
+    }
+    plan->stats.h2d_bytes += (int64_t) bytes;
+}
+
+static void stage_out(sdp_GridderUvwEsFft* plan, const EsBuffer* b,
+        sdp_Mem* m, sdp_Error* status)
+{
+    const size_t bytes = mem_bytes(m);
+    if (*status || bytes == 0) return;
+    const cudaError_t err = cudaMemcpyAsync(sdp_mem_data(m), b->ptr, bytes,
+            cudaMemcpyDeviceToHost, plan->stream);
+    if (err != cudaSuccess)
+    {
+        *status = SDP_ERR_MEM_COPY_FAILURE;
+        SDP_LOG_CRITICAL("cudaMemcpy error: %s", cudaGetErrorString(err));
+        (void) cudaGetLastError();
+        return;
+    }
+    plan->stats.d2h_bytes += (int64_t) bytes;
+}
+
+/* Device views of the five arrays; host arrays are copied in (extension over
+ * the reference, which would fail with SDP_ERR_MEM_LOCATION). */
+static void resolve_arrays(sdp_GridderUvwEsFft* plan, const sdp_Mem* uvw,
+        const sdp_Mem* freq_hz, const sdp_Mem* vis, const sdp_Mem* weight,
+        const sdp_Mem* dirty_image, int need_weight, EsArrays* a,
+        sdp_Error* status)
+{
+    memset(a, 0, sizeof(*a));
+    if (*status) return;
+    if (sdp_mem_location(uvw) == SDP_MEM_GPU)
+    {
+        a->uvw = sdp_mem_data_const(uvw);
+        a->freq = sdp_mem_data_const(freq_hz);
+        a->vis = (void*) sdp_mem_data_const(vis);
+        a->weight = sdp_mem_data_const(weight);
+        a->dirty = (void*) sdp_mem_data_const(dirty_image);
+        return;
+    }
+    a->staged = 1;
+    stage_in(plan, &plan->st_uvw, uvw, status);
+    stage_in(plan, &plan->st_freq, freq_hz, status);
+    stage_in(plan, &plan->st_vis, vis, status);
+    if (need_weight) stage_in(plan, &plan->st_weight, weight, status);
+    stage_in(plan, &plan->st_dirty, dirty_image, status);
+    a->uvw = plan->st_uvw.ptr;
+    a->freq = plan->st_freq.ptr;
+    a->vis = plan->st_vis.ptr;
+    a->weight = plan->st_weight.ptr;
+    a->dirty = plan->st_dirty.ptr;
+}
+
+/* -------------------------------------------------------------- presort */
+
+static int bits_for(uint64_t max_value)
+{
+    int bits = 1;
+    while (bits < 64 && (max_value >> bits) != 0) bits++;
+    return bits;
+}
+
+/* Expands the visibilities into (tile, plane)-sorted records for the owned
+ * plane range. Leaves keys in keys_b, records in records; sets *num_entries. */
+static void presort(sdp_GridderUvwEsFft* plan, const EsArrays* a,
+        int for_gridding, int64_t* num_entries, sdp_Error* status)
+{
+    *num_entries = 0;
+    if (*status) return;
+    EsGeom* g = &plan->geom;
+    cudaStream_t s = plan->stream;
+    const int64_t nvis = (int64_t) g->num_rows * g->num_chan;
+    const size_t ntiles = (size_t) g->ntile * g->ntile;
+    buffer_reserve(&plan->tile_start, (ntiles + 2) * sizeof(uint32_t), status);
+    buffer_reserve(&plan->counts, (size_t) nvis + 16, status);
+    buffer_reserve(&plan->offsets, ((size_t) nvis + 1) * sizeof(uint32_t),
+            status);
+    if (*status) return;
+    if (nvis == 0 || g->plane_begin >= g->plane_end)
+    {
+        ES_CUDA(es_launch_tile_bounds(g, 0, 0, (uint32_t*) plan->tile_start.ptr, s));
+        return;
+    }
+
+    /* entries per visibility -> offsets (the extra zero count makes the
+     * total come out as offsets[nvis]) */
+    ES_CUDA(cudaMemsetAsync((uint8_t*) plan->counts.ptr + nvis, 0, 1, s));
+    ES_CUDA(es_launch_count_entries(g, a->uvw, a->freq,
+            (uint8_t*) plan->counts.ptr, s));
+    size_t scan_bytes = 0;
+    ES_CUDA(es_scan_counts((const uint8_t*) plan->counts.ptr,
+            (uint32_t*) plan->offsets.ptr, nvis + 1, 0, &scan_bytes, s));
+    buffer_reserve(&plan->sort_temp, scan_bytes, status);
+    if (*status) return;
+    scan_bytes = plan->sort_temp.bytes;
+    ES_CUDA(es_scan_counts((const uint8_t*) plan->counts.ptr,
+            (uint32_t*) plan->offsets.ptr, nvis + 1, plan->sort_temp.ptr,
+            &scan_bytes, s));
+    uint32_t total = 0;
+    ES_CUDA(cudaMemcpyAsync(&total, (const uint32_t*) plan->offsets.ptr + nvis,
+            sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+    ES_CUDA(cudaStreamSynchronize(s));
+    const int64_t m = (int64_t) total;
+    plan->stats.kernel_launches += 1;
+    if (m == 0)
+    {
+        ES_CUDA(es_launch_tile_bounds(g, 0, 0, (uint32_t*) plan->tile_start.ptr, s));
+        return;
+    }
+
+    const size_t rec_bytes = es_record_bytes(g->is_double);
+    buffer_reserve(&plan->keys_a, (size_t) m * sizeof(uint64_t), status);
+    buffer_reserve(&plan->keys_b, (size_t) m * sizeof(uint64_t), status);
+    buffer_reserve(&plan->vals_a, (size_t) m * sizeof(uint32_t), status);
+    buffer_reserve(&plan->vals_b, (size_t) m * sizeof(uint32_t), status);
+    buffer_reserve(&plan->records, (size_t) m * rec_bytes, status);
+    if (*status) return;
+
+    ES_CUDA(es_launch_emit_entries(g, a->uvw, a->freq,
+            (const uint32_t*) plan->offsets.ptr, (uint64_t*) plan->keys_a.ptr,
+            (uint32_t*) plan->vals_a.ptr, s));
+    const uint64_t pk = (uint64_t) (g->plane_end - g->plane_begin);
+    const int end_bit = bits_for((uint64_t) ntiles * pk);
+    size_t sort_bytes = 0;
+    ES_CUDA(es_sort_entries((const uint64_t*) plan->keys_a.ptr,
+            (uint64_t*) plan->keys_b.ptr, (const uint32_t*) plan->vals_a.ptr,
+            (uint32_t*) plan->vals_b.ptr, m, end_bit, 0, &sort_bytes, s));
+    buffer_reserve(&plan->sort_temp, sort_bytes, status);
+    if (*status) return;
+    sort_bytes = plan->sort_temp.bytes;
+    ES_CUDA(es_sort_entries((const uint64_t*) plan->keys_a.ptr,
+            (uint64_t*) plan->keys_b.ptr, (const uint32_t*) plan->vals_a.ptr,
+            (uint32_t*) plan->vals_b.ptr, m, end_bit, plan->sort_temp.ptr,
+            &sort_bytes, s));
+    ES_CUDA(es_launch_tile_bounds(g, (const uint64_t*) plan->keys_b.ptr, m,
+            (uint32_t*) plan->tile_start.ptr, s));
+    ES_CUDA(es_launch_build_records(g, a->uvw, a->freq,
+            for_gridding ? a->vis : 0, for_gridding ? a->weight : 0,
+            (const uint64_t*) plan->keys_b.ptr,
+            (const uint32_t*) plan->vals_b.ptr, m, plan->records.ptr, s));
+    plan->stats.kernel_launches += 3;
+    *num_entries = m;
+}
+
+/* --------------------------------------------------------------- timing */
+
+static void events_begin(sdp_GridderUvwEsFft* plan)
+{
+    memset(&plan->stats, 0, sizeof(plan->stats));
+    plan->stats.plane_batch = plan->plane_batch;
+    plan->stats.timing_enabled = plan->timing;
+    if (plan->timing && !plan->have_events)
+    {
+        int ok = 1;
+        for (int k = 0; k < 8; ++k)
+            if (cudaEventCreate(&plan->ev[k]) != cudaSuccess) ok = 0;
+        plan->have_events = ok;
+        if (!ok) (void) cudaGetLastError();
+    }
+    if (plan->timing && plan->have_events)
+        (void) cudaEventRecord(plan->ev[0], plan->stream);
+}
+
+static void event_mark(sdp_GridderUvwEsFft* plan, int k)
+{
+    if (plan->timing && plan->have_events)
+        (void) cudaEventRecord(plan->ev[k], plan->stream);
+}
+
+static double event_ms(sdp_GridderUvwEsFft* plan, int from, int to)
+{
+    float ms = 0.0f;
+    if (cudaEventElapsedTime(&ms, plan->ev[from], plan->ev[to]) != cudaSuccess)
+        (void) cudaGetLastError();
+    return (double) ms;
+}
+
+/* ------------------------------------------------------------- gridding */
+
+void sdp_grid_uvw_es_fft(sdp_GridderUvwEsFft* plan, const sdp_Mem* uvw,
+        const sdp_Mem* freq_hz, const sdp_Mem* vis, const sdp_Mem* weight,
+        sdp_Mem* dirty_image, sdp_Error* status)
+{
+    SDP_LOG_DEBUG("Executing sdp_GridderUvwEsFft...");
+    if (*status || !plan) return;
+    check_parameters(plan->pixsize_x_rad, plan->pixsize_y_rad, status);
+    if (*status) return;
+    check_buffers(uvw, freq_hz, vis, weight, dirty_image, 0, status);
+    check_against_plan(plan, vis, dirty_image, status);
+    if (*status) return;
+
+    EsGeom* g = &plan->geom;
+    g->plane_begin = plan->plane_begin;
+    g->plane_end = plan->plane_end;
+    cudaStream_t s = plan->stream;
+    events_begin(plan);
+
+    EsArrays a;
+    resolve_arrays(plan, uvw, freq_hz, vis, weight, dirty_image, 1, &a, status);
+    if (*status) return;
+
+    int64_t m = 0;
+    presort(plan, &a, 1, &m, status);
+    if (*status) return;
+    plan->stats.num_entries = m;
+    event_mark(plan, 1);
+
+    for (int first = g->plane_begin; first < g->plane_end;
+            first += plan->plane_batch)
+    {
+        int nb = g->plane_end - first;
+        if (nb > plan->plane_batch) nb = plan->plane_batch;
+        ES_CUDA(es_launch_scatter(g, plan->records.ptr,
+                (const uint64_t*) plan->keys_b.ptr,
+                (const uint32_t*) plan->tile_start.ptr, first, nb,
+                plan->planes.ptr, s));
+        fft_exec(plan, nb, 0, status); /* CUFFT_INVERSE, es_fft.cpp:568 */
+        if (*status) return;
+        ES_CUDA(es_launch_apply_screen(g, plan->planes.ptr, first, nb,
+                a.dirty, s));
+        plan->stats.kernel_launches += 2;
+        plan->stats.planes_processed += nb;
+    }
+    event_mark(plan, 2);
+    if (plan->apply_correction)
+    {
+        ES_CUDA(es_launch_correct(g, a.dirty, plan->d_quad_kernel,
+                plan->d_quad_nodes, plan->d_quad_weights, plan->d_conv_corr,
+                s));
+        plan->stats.kernel_launches += 1;
+    }
+    if (a.staged)
+    {
+        stage_out(plan, &plan->st_dirty, dirty_image, status);
+        ES_CUDA(cudaStreamSynchronize(s));
+    }
+    event_mark(plan, 3);
+    if (plan->timing && plan->have_events)
+    {
+        ES_CUDA(cudaEventSynchronize(plan->ev[3]));
+        plan->stats.ms_presort = event_ms(plan, 0, 1);
+        plan->stats.ms_total = event_ms(plan, 0, 3);
+    }
+}
+
+/* ----------------------------------------------------------- degridding */
+
+void sdp_ifft_degrid_uvw_es(sdp_GridderUvwEsFft* plan, const sdp_Mem* uvw,
+        const sdp_Mem* freq_hz, sdp_Mem* vis, const sdp_Mem* weight,
+        sdp_Mem* dirty_image, sdp_Error* status)
+{
+    SDP_LOG_DEBUG("Executing sdp_GridderUvwEsFft...");
+    if (*status || !plan) return;
+    check_parameters(plan->pixsize_x_rad, plan->pixsize_y_rad, status);
+    if (*status) return;
+    check_buffers(uvw, freq_hz, vis, weight, dirty_image, 1, status);
+    check_against_plan(plan, vis, dirty_image, status);
+    if (*status) return;
+
+    EsGeom* g = &plan->geom;
+    g->plane_begin = plan->plane_begin;
+    g->plane_end = plan->plane_end;
+    cudaStream_t s = plan->stream;
+    events_begin(plan);
+
+    EsArrays a;
+    resolve_arrays(plan, uvw, freq_hz, vis, weight, dirty_image, 0, &a, status);
+    if (*status) return;
+
+    int64_t m = 0;
+    presort(plan, &a, 0, &m, status);
+    if (*status) return;
+    plan->stats.num_entries = m;
+    const size_t cplx = 2 * real_bytes(plan);
+    buffer_reserve(&plan->acc, (size_t) (m > 0 ? m : 1) * cplx, status);
+    if (*status) return;
+    ES_CUDA(cudaMemsetAsync(plan->acc.ptr, 0, (size_t) (m > 0 ? m : 1) * cplx, s));
+    event_mark(plan, 1);
+
+    /* grid correction in place on the caller's image (es_fft.cpp:789-825) */
+    if (plan->apply_correction)
+    {
+        ES_CUDA(es_launch_correct(g, a.dirty, plan->d_quad_kernel,
+                plan->d_quad_nodes, plan->d_quad_weights, plan->d_conv_corr,
+                s));
+        plan->stats.kernel_launches += 1;
+    }
+    for (int first = g->plane_begin; first < g->plane_end;
+            first += plan->plane_batch)
+    {
+        int nb = g->plane_end - first;
+        if (nb > plan->plane_batch) nb = plan->plane_batch;
+        ES_CUDA(es_launch_reverse_screen(g, a.dirty, first, nb,
+                plan->planes.ptr, s));
+        fft_exec(plan, nb, 1, status); /* CUFFT_FORWARD, es_fft.cpp:782 */
+        if (*status) return;
+        ES_CUDA(es_launch_gather(g, plan->records.ptr,
+                (const uint64_t*) plan->keys_b.ptr,
+                (const uint32_t*) plan->tile_start.ptr, first, nb,
+                plan->planes.ptr, plan->acc.ptr, s));
+        plan->stats.kernel_launches += 3;
+        plan->stats.planes_processed += nb;
+    }
+    event_mark(plan, 2);
+    ES_CUDA(es_launch_finish_degrid(g, plan->records.ptr, plan->acc.ptr, m,
+            a.vis, s));
+    plan->stats.kernel_launches += 1;
+    if (a.staged)
+    {
+        stage_out(plan, &plan->st_vis, vis, status);
+        stage_out(plan, &plan->st_dirty, dirty_image, status);
+        ES_CUDA(cudaStreamSynchronize(s));
+    }
+    event_mark(plan, 3);
+    if (plan->timing && plan->have_events)
+    {
+        ES_CUDA(cudaEventSynchronize(plan->ev[3]));
+        plan->stats.ms_presort = event_ms(plan, 0, 1);
+        plan->stats.ms_total = event_ms(plan, 0, 3);
+    }
+}
+
+/* ----------------------------------------------------------- extensions */
+
+void sdp_gridder_uvw_es_fft_correct_image(sdp_GridderUvwEsFft* plan,
+        sdp_Mem* dirty_image, sdp_Error* status)
+{
+    if (*status || !plan) return;
+    if (sdp_mem_shape_dim(dirty_image, 0) != plan->info.image_size ||
+            sdp_mem_shape_dim(dirty_image, 1) != plan->info.image_size ||
+            (sdp_mem_is_double(dirty_image) != 0) != (plan->info.is_double != 0)
+            || sdp_mem_is_complex(dirty_image) ||
+            !sdp_mem_is_c_contiguous(dirty_image))
+    {
+        *status = SDP_ERR_INVALID_ARGUMENT;
+        SDP_LOG_ERROR("Image does not match the plan.");
+        return;
+    }
+    void* d = sdp_mem_data(dirty_image);
+    const int staged = sdp_mem_location(dirty_image) != SDP_MEM_GPU;
+    if (staged)
+    {
+        stage_in(plan, &plan->st_dirty, dirty_image, status);
+        if (*status) return;
+        d = plan->st_dirty.ptr;
+    }
+    ES_CUDA(es_launch_correct(&plan->geom, d, plan->d_quad_kernel,
+            plan->d_quad_nodes, plan->d_quad_weights, plan->d_conv_corr,
+            plan->stream));
+    if (staged)
+    {
+        stage_out(plan, &plan->st_dirty, dirty_image, status);
+        ES_CUDA(cudaStreamSynchronize(plan->stream));
+    }
+}
+
+void sdp_gridder_uvw_es_fft_plane_histogram(sdp_GridderUvwEsFft* plan,
+        const sdp_Mem* uvw, const sdp_Mem* freq_hz, int64_t* counts,
+        sdp_Error* status)
+{
+    if (*status || !plan || !counts) return;
+    if (sdp_mem_location(uvw) != sdp_mem_location(freq_hz))
+    {
+        *status = SDP_ERR_MEM_LOCATION;
+        SDP_LOG_ERROR("Memory location mismatch.");
+        return;
+    }
+    if (sdp_mem_shape_dim(uvw, 0) != plan->info.num_rows ||
+            sdp_mem_shape_dim(uvw, 1) != 3 ||
+            sdp_mem_shape_dim(freq_hz, 0) != plan->info.num_chan ||
+            (sdp_mem_is_double(uvw) != 0) != (plan->info.is_double != 0) ||
+            (sdp_mem_is_double(freq_hz) != 0) != (plan->info.is_double != 0))
+    {
+        *status = SDP_ERR_INVALID_ARGUMENT;
+        SDP_LOG_ERROR("uvw / freq_hz do not match the plan.");
+        return;
+    }
+    EsGeom g = plan->geom;
+    g.plane_begin = 0;
+    g.plane_end = g.num_planes;
+    const void* d_uvw = sdp_mem_data_const(uvw);
+    const void* d_freq = sdp_mem_data_const(freq_hz);
+    if (sdp_mem_location(uvw) != SDP_MEM_GPU)
+    {
+        stage_in(plan, &plan->st_uvw, uvw, status);
+        stage_in(plan, &plan->st_freq, freq_hz, status);
+        if (*status) return;
+        d_uvw = plan->st_uvw.ptr;
+        d_freq = plan->st_freq.ptr;
+    }
+    const size_t bytes = (size_t) g.num_planes * sizeof(unsigned long long);
+    buffer_reserve(&plan->sort_temp, bytes, status);
+    if (*status) return;
+    ES_CUDA(cudaMemsetAsync(plan->sort_temp.ptr, 0, bytes, plan->stream));
+    ES_CUDA(es_launch_plane_histogram(&g, d_uvw, d_freq,
+            (unsigned long long*) plan->sort_temp.ptr, plan->stream));
+    ES_CUDA(cudaMemcpyAsync(counts, plan->sort_temp.ptr, bytes,
+            cudaMemcpyDeviceToHost, plan->stream));
+    ES_CUDA(cudaStreamSynchronize(plan->stream));
+}

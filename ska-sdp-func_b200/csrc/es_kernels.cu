@@ -1,0 +1,972 @@
+/*
+ * sm_100a kernels of the B200-native w-stacking ES gridder / degridder and
+ * their C-ABI launchers (see es_device.h).
+ *
+ * What the reference does with one thread per visibility, global atomics and
+ * a full re-scan of every visibility for every w-plane
+ * (src/ska-sdp-func/grid_data/sdp_gridder_uvw_es_fft_kernels.cu:126-270) is
+ * done here as:
+ *   presort   - every visibility is expanded into one record per 64x64 uv tile
+ *               its footprint overlaps; records are radix sorted by
+ *               (tile, first owned w-plane), so the records that touch plane p
+ *               of tile t are ONE contiguous range found by binary search;
+ *   scatter   - one CTA per (tile, plane): the tile is accumulated in shared
+ *               memory without atomics (each warp owns a band of 16 rows, the
+ *               lanes of a warp own distinct cells of one footprint) and then
+ *               flushed once with coalesced 16-byte stores. Every cell of the
+ *               plane is written exactly once, so the reference's per-plane
+ *               cudaMemset (es_fft.cpp:586) disappears;
+ *   gather    - the same ranges, one thread per record, plain loads;
+ *   w-screen  - one thread per 4 mirror pixels as in kernels.cu:429-679, but
+ *               looping over a BATCH of resident planes with register
+ *               accumulators (one image read-modify-write per batch), and with
+ *               the phase reduced in fp64 before an fp32 sincospi.
+ * All coordinates (grid position, w-plane position, w-screen phase) are fp64
+ * in both precisions; fp32 is used for kernel weights, accumulation and the
+ * FFT only.
+ */
+#include <stdint.h>
+
+#include <cuda_runtime.h>
+#include <cub/cub.cuh>
+
+#include "es_device.h"
+
+#define ES_C0 299792458.0           /* kernels.cu:159 */
+#define ES_PI 3.1415926535897931    /* kernels.cu:10 */
+
+namespace {
+
+/* ------------------------------------------------------------- records */
+
+struct __align__(16) EsRecF
+{
+    short lu0, lv0;   /* first footprint slot, in tile-local cell indices */
+    int p0;           /* first (unclipped) w-plane: ceil(pos_w - W/2) */
+    float du, dv, dw; /* (first slot - position) in u, v, w: in [-W/2, -W/2 + 1) */
+    float vre, vim;   /* scatter: weighted visibility; gather: vre = flip */
+    unsigned int idx; /* row * num_chan + chan */
+};
+
+struct __align__(16) EsRecD
+{
+    short lu0, lv0;
+    int p0;
+    double du, dv, dw;
+    double vre, vim;
+    unsigned int idx;
+    unsigned int pad0;
+    double pad1;
+};
+
+static_assert(sizeof(EsRecF) == 32, "fp32 record must be 32 bytes");
+static_assert(sizeof(EsRecD) == 64, "fp64 record must be 64 bytes");
+
+template<typename T> struct Prec;
+template<> struct Prec<float>
+{
+    typedef float2 T2;
+    typedef EsRecF Rec;
+};
+template<> struct Prec<double>
+{
+    typedef double2 T2;
+    typedef EsRecD Rec;
+};
+
+/* ------------------------------------------------------------ ES kernel */
+
+/* psi(x) = x^2 > 1 ? 0 : exp(beta (sqrt(1 - x^2) - 1)), kernels.cu:97-102 */
+__device__ __forceinline__ float es_psi(float beta, float x)
+{
+    const float t = 1.0f - x * x;
+    return (t < 0.0f) ? 0.0f : __expf(beta * (sqrtf(t) - 1.0f));
+}
+
+__device__ __forceinline__ double es_psi(double beta, double x)
+{
+    const double t = 1.0 - x * x;
+    return (t < 0.0) ? 0.0 : exp(beta * (sqrt(t) - 1.0));
+}
+
+/* Where one visibility lands. Restates kernels.cu:157-196 with fp64
+ * coordinates; the footprint is described by its first slot (iu0, iv0, p0)
+ * and the offsets du = iu0 - pos_u ...: slot k sits at (k + du) / (W/2) in
+ * kernel units, slots 0..W (the last one has weight 0 unless du == -W/2). */
+struct Foot
+{
+    int iu0, iv0, p0;
+    int u_lo, u_hi, v_lo, v_hi, p_lo, p_hi;
+    double du, dv, dw, flip;
+    bool valid;
+};
+
+template<typename T>
+__device__ __forceinline__ Foot es_footprint(const EsGeom& g,
+        const T* __restrict__ uvw, const T* __restrict__ freq, int row, int chan)
+{
+    Foot f;
+    const double u = (double) uvw[3 * (size_t) row];
+    const double v = (double) uvw[3 * (size_t) row + 1];
+    const double w = (double) uvw[3 * (size_t) row + 2];
+    const double hs = 0.5 * (double) g.support;
+    f.flip = (g.do_wstacking && w < 0.0) ? -1.0 : 1.0;
+    const double inv_wavelength = f.flip * (double) freq[chan] / ES_C0;
+    const double pos_u = u * inv_wavelength * g.uv_scale;
+    const double pos_v = v * inv_wavelength * g.uv_scale;
+    const double pos_w = g.do_wstacking ?
+            (w * inv_wavelength - g.min_plane_w) * g.w_scale : 0.0;
+    const double cu = ceil(pos_u - hs), cv = ceil(pos_v - hs);
+    const double cw = ceil(pos_w - hs);
+    const bool finite = isfinite(pos_u) && isfinite(pos_v) && isfinite(pos_w);
+    f.iu0 = (int) cu; f.iv0 = (int) cv; f.p0 = (int) cw;
+    f.du = cu - pos_u; f.dv = cv - pos_v; f.dw = cw - pos_w;
+    const int grid_min = -(g.grid_size / 2);
+    const int grid_max = (g.grid_size - 1) / 2;
+    f.u_lo = max(f.iu0, grid_min);
+    f.u_hi = min((int) floor(pos_u + hs), grid_max);
+    f.v_lo = max(f.iv0, grid_min);
+    f.v_hi = min((int) floor(pos_v + hs), grid_max);
+    f.p_lo = max(f.p0, g.plane_begin);
+    f.p_hi = min((int) floor(pos_w + hs), g.plane_end - 1);
+    f.valid = finite && f.u_lo <= f.u_hi && f.v_lo <= f.v_hi &&
+            f.p_lo <= f.p_hi;
+    return f;
+}
+
+/* ------------------------------------------------------------- presort */
+
+template<typename T>
+__global__ void __launch_bounds__(256) es_count_entries_kernel(EsGeom g,
+        const T* __restrict__ uvw, const T* __restrict__ freq,
+        uint8_t* __restrict__ counts)
+{
+    const int64_t nvis = (int64_t) g.num_rows * g.num_chan;
+    const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nvis) return;
+    const int row = (int) (i / g.num_chan), chan = (int) (i % g.num_chan);
+    const Foot f = es_footprint<T>(g, uvw, freq, row, chan);
+    int n = 0;
+    if (f.valid)
+    {
+        const int half = g.grid_size / 2;
+        const int tu = (f.u_hi + half) / ES_TILE - (f.u_lo + half) / ES_TILE + 1;
+        const int tv = (f.v_hi + half) / ES_TILE - (f.v_lo + half) / ES_TILE + 1;
+        n = tu * tv;
+    }
+    counts[i] = (uint8_t) n;
+}
+
+template<typename T>
+__global__ void __launch_bounds__(256) es_emit_entries_kernel(EsGeom g,
+        const T* __restrict__ uvw, const T* __restrict__ freq,
+        const uint32_t* __restrict__ offsets, uint64_t* __restrict__ keys,
+        uint32_t* __restrict__ vals)
+{
+    const int64_t nvis = (int64_t) g.num_rows * g.num_chan;
+    const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nvis) return;
+    const int row = (int) (i / g.num_chan), chan = (int) (i % g.num_chan);
+    const Foot f = es_footprint<T>(g, uvw, freq, row, chan);
+    if (!f.valid) return;
+    const int half = g.grid_size / 2;
+    const uint64_t pk = (uint64_t) (g.plane_end - g.plane_begin);
+    const uint64_t kp = (uint64_t) (f.p_lo - g.plane_begin);
+    uint32_t slot = offsets[i];
+    for (int tu = (f.u_lo + half) / ES_TILE; tu <= (f.u_hi + half) / ES_TILE; ++tu)
+    {
+        for (int tv = (f.v_lo + half) / ES_TILE; tv <= (f.v_hi + half) / ES_TILE; ++tv)
+        {
+            keys[slot] = (uint64_t) (tu * g.ntile + tv) * pk + kp;
+            vals[slot] = (uint32_t) i;
+            ++slot;
+        }
+    }
+}
+
+struct CastU8
+{
+    __host__ __device__ __forceinline__ uint32_t operator()(const uint8_t& x) const
+    {
+        return (uint32_t) x;
+    }
+};
+
+__global__ void __launch_bounds__(256) es_tile_bounds_kernel(EsGeom g,
+        const uint64_t* __restrict__ keys, int64_t num_entries,
+        uint32_t* __restrict__ tile_start)
+{
+    const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= num_entries) return;
+    const uint64_t pk = (uint64_t) (g.plane_end - g.plane_begin);
+    const int64_t t = (int64_t) (keys[i] / pk);
+    const int64_t tprev = (i > 0) ? (int64_t) (keys[i - 1] / pk) : -1;
+    for (int64_t x = tprev + 1; x <= t; ++x) tile_start[x] = (uint32_t) i;
+    if (i == num_entries - 1)
+    {
+        const int64_t ntiles = (int64_t) g.ntile * g.ntile;
+        for (int64_t x = t + 1; x <= ntiles; ++x)
+            tile_start[x] = (uint32_t) num_entries;
+    }
+}
+
+template<typename T>
+__global__ void __launch_bounds__(256) es_build_records_kernel(EsGeom g,
+        const T* __restrict__ uvw, const T* __restrict__ freq,
+        const typename Prec<T>::T2* __restrict__ vis,
+        const T* __restrict__ weight, const uint64_t* __restrict__ keys,
+        const uint32_t* __restrict__ vals, int64_t num_entries,
+        typename Prec<T>::Rec* __restrict__ records)
+{
+    const int64_t e = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= num_entries) return;
+    const uint32_t idx = vals[e];
+    const int row = (int) (idx / (uint32_t) g.num_chan);
+    const int chan = (int) (idx % (uint32_t) g.num_chan);
+    const Foot f = es_footprint<T>(g, uvw, freq, row, chan);
+    const uint64_t pk = (uint64_t) (g.plane_end - g.plane_begin);
+    const int tile_id = (int) (keys[e] / pk);
+    const int tu = tile_id / g.ntile, tv = tile_id % g.ntile;
+    const int half = g.grid_size / 2;
+    typename Prec<T>::Rec r;
+    r.lu0 = (short) (f.iu0 + half - tu * ES_TILE);
+    r.lv0 = (short) (f.iv0 + half - tv * ES_TILE);
+    r.p0 = f.p0;
+    r.du = (T) f.du; r.dv = (T) f.dv; r.dw = (T) f.dw;
+    r.idx = idx;
+    if (vis)
+    {
+        /* kernels.cu:163-168 */
+        const typename Prec<T>::T2 v = vis[idx];
+        const T wt = weight[idx];
+        r.vre = v.x * wt;
+        r.vim = v.y * wt * (T) f.flip;
+    }
+    else
+    {
+        r.vre = (T) f.flip;
+        r.vim = (T) 0;
+    }
+    records[e] = r;
+}
+
+template<typename T>
+__global__ void __launch_bounds__(256) es_plane_histogram_kernel(EsGeom g,
+        const T* __restrict__ uvw, const T* __restrict__ freq,
+        unsigned long long* __restrict__ hist)
+{
+    const int64_t nvis = (int64_t) g.num_rows * g.num_chan;
+    const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nvis) return;
+    const int row = (int) (i / g.num_chan), chan = (int) (i % g.num_chan);
+    const Foot f = es_footprint<T>(g, uvw, freq, row, chan);
+    if (!f.valid) return;
+    atomicAdd(&hist[f.p_lo], 1ULL);
+}
+
+/* Range of sorted entries of `tile_id` that can touch `plane`: first owned
+ * plane in [plane - W, plane]. Every thread computes it (broadcast loads). */
+__device__ __forceinline__ void es_entry_range(const EsGeom& g,
+        const uint64_t* __restrict__ keys,
+        const uint32_t* __restrict__ tile_start, int tile_id, int plane,
+        uint32_t& a, uint32_t& b)
+{
+    uint32_t lo = tile_start[tile_id];
+    const uint32_t hi = tile_start[tile_id + 1];
+    a = b = lo;
+    if (lo == hi) return;
+    const uint64_t pk = (uint64_t) (g.plane_end - g.plane_begin);
+    const uint64_t base = (uint64_t) tile_id * pk;
+    const int kp_hi = plane - g.plane_begin;
+    const int kp_lo = max(kp_hi - g.support, 0);
+    const uint64_t key_lo = base + (uint64_t) kp_lo;
+    const uint64_t key_hi = base + (uint64_t) kp_hi; /* inclusive */
+    uint32_t l = lo, h = hi;
+    while (l < h) /* first key >= key_lo */
+    {
+        const uint32_t m = l + ((h - l) >> 1);
+        if (keys[m] < key_lo) l = m + 1; else h = m;
+    }
+    a = l;
+    h = hi;
+    while (l < h) /* first key > key_hi */
+    {
+        const uint32_t m = l + ((h - l) >> 1);
+        if (keys[m] <= key_hi) l = m + 1; else h = m;
+    }
+    b = l;
+}
+
+/* ------------------------------------------------------------- scatter */
+
+#define ES_SCATTER_THREADS 128
+#define ES_BAND (ES_TILE / (ES_SCATTER_THREADS / 32)) /* rows owned per warp */
+
+/* CS: column slots per row step (16: two rows per step, support <= 15;
+ * 32: one row per step, support 16). */
+template<typename T, int CS>
+__global__ void __launch_bounds__(ES_SCATTER_THREADS) es_scatter_kernel(
+        EsGeom g, const typename Prec<T>::Rec* __restrict__ records,
+        const uint64_t* __restrict__ keys,
+        const uint32_t* __restrict__ tile_start, int first_plane,
+        typename Prec<T>::T2* __restrict__ planes)
+{
+    typedef typename Prec<T>::T2 T2;
+    typedef typename Prec<T>::Rec Rec;
+    extern __shared__ __align__(16) unsigned char es_smem[];
+    T2* tile = (T2*) es_smem; /* [ES_TILE][ES_TILE] */
+    __shared__ int s_pos[ES_SCATTER_THREADS];
+    __shared__ T s_du[ES_SCATTER_THREADS], s_dv[ES_SCATTER_THREADS];
+    __shared__ T s_vre[ES_SCATTER_THREADS], s_vim[ES_SCATTER_THREADS];
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tile_id = blockIdx.x;
+    const int plane = first_plane + blockIdx.y;
+    const int tu = tile_id / g.ntile, tv = tile_id % g.ntile;
+    const int gsz = g.grid_size;
+    const int rows_valid = min(ES_TILE, gsz - tu * ES_TILE);
+    const int cols_valid = min(ES_TILE, gsz - tv * ES_TILE);
+    T2* out = planes + (size_t) blockIdx.y * gsz * gsz +
+            (size_t) (tu * ES_TILE) * gsz + (size_t) (tv * ES_TILE);
+
+    uint32_t a, b;
+    es_entry_range(g, keys, tile_start, tile_id, plane, a, b);
+
+    /* 16-byte vectors of the tile rows: VEC cells each. */
+    constexpr int VEC = 16 / (int) sizeof(T2);
+    constexpr int VPR = ES_TILE / VEC; /* vectors per tile row */
+    const int vec_valid = cols_valid / VEC; /* grid_size is even */
+
+    if (a == b)
+    {
+        /* nothing lands here on this plane: the fused "memset" */
+        const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int v = tid; v < ES_TILE * VPR; v += ES_SCATTER_THREADS)
+        {
+            const int r = v / VPR, c = v % VPR;
+            if (r < rows_valid && c < vec_valid)
+                *reinterpret_cast<float4*>(out + (size_t) r * gsz + c * VEC) = zero;
+        }
+        return;
+    }
+
+    for (int v = tid; v < ES_TILE * VPR; v += ES_SCATTER_THREADS)
+        reinterpret_cast<float4*>(tile)[v] = make_float4(0.f, 0.f, 0.f, 0.f);
+    __syncthreads();
+
+    const int w_sup = g.support;
+    const T beta = (T) g.beta;
+    const T inv_hs = (T) (2.0 / (double) w_sup);
+    const int band_lo = warp * ES_BAND;
+    const int band_hi = min(band_lo + ES_BAND, rows_valid) - 1;
+    const int c = lane % CS;       /* my column slot */
+    const int rsub = lane / CS;    /* my row within a step */
+    constexpr int RPS = 32 / CS;   /* rows per step */
+
+    for (uint32_t chunk = a; chunk < b; chunk += ES_SCATTER_THREADS)
+    {
+        const int n = (int) min((uint32_t) ES_SCATTER_THREADS, b - chunk);
+        if (tid < n)
+        {
+            const Rec r = records[chunk + tid];
+            const int dp = plane - r.p0;
+            /* kernels.cu:219-221; dp > W cannot carry weight */
+            const T kw = (dp >= 0 && dp <= w_sup) ?
+                    es_psi(beta, ((T) dp + r.dw) * inv_hs) : (T) 0;
+            s_pos[tid] = ((int) r.lu0 << 16) | ((int) r.lv0 & 0xffff);
+            s_du[tid] = r.du;
+            s_dv[tid] = r.dv;
+            s_vre[tid] = r.vre * kw;
+            s_vim[tid] = r.vim * kw;
+        }
+        __syncthreads();
+        for (int e = 0; e < n; ++e)
+        {
+            const int pos = s_pos[e];
+            const int lu0 = pos >> 16;
+            const int r_lo = max(lu0, band_lo);
+            const int r_hi = min(lu0 + w_sup, band_hi);
+            if (r_lo > r_hi) continue; /* warp-uniform */
+            const int lv0 = (int) (short) (pos & 0xffff);
+            const int col = lv0 + c;
+            const bool col_ok = (c <= w_sup) && col >= 0 && col < cols_valid;
+            /* kernels.cu:201-213: one u weight per lane 0..W, one v weight
+             * per column slot */
+            const T ku_lane = (lane <= w_sup) ?
+                    es_psi(beta, ((T) lane + s_du[e]) * inv_hs) : (T) 0;
+            T kvc = col_ok ? es_psi(beta, ((T) c + s_dv[e]) * inv_hs) : (T) 0;
+            if (col & 1) kvc = -kvc; /* (-1)^(gu+gv), kernels.cu:233-235 */
+            const T pre = s_vre[e] * kvc, pim = s_vim[e] * kvc;
+            for (int r0 = r_lo; r0 <= r_hi; r0 += RPS)
+            {
+                const int r = r0 + rsub;
+                T ku = __shfl_sync(0xffffffffu, ku_lane, min(r - lu0, 31));
+                if (r & 1) ku = -ku;
+                if (col_ok && r <= r_hi)
+                {
+                    T2 cell = tile[r * ES_TILE + col];
+                    cell.x += pre * ku;
+                    cell.y += pim * ku;
+                    tile[r * ES_TILE + col] = cell;
+                }
+            }
+            __syncwarp();
+        }
+        __syncthreads();
+    }
+
+    for (int v = tid; v < ES_TILE * VPR; v += ES_SCATTER_THREADS)
+    {
+        const int r = v / VPR, cv = v % VPR;
+        if (r < rows_valid && cv < vec_valid)
+            *reinterpret_cast<float4*>(out + (size_t) r * gsz + cv * VEC) =
+                    reinterpret_cast<const float4*>(tile)[v];
+    }
+}
+
+/* -------------------------------------------------------------- gather */
+
+#define ES_GATHER_THREADS 128
+
+/* NS: footprint slots per axis handled (support + 1 <= NS). */
+template<typename T, int NS>
+__global__ void __launch_bounds__(ES_GATHER_THREADS) es_gather_kernel(
+        EsGeom g, const typename Prec<T>::Rec* __restrict__ records,
+        const uint64_t* __restrict__ keys,
+        const uint32_t* __restrict__ tile_start, int first_plane,
+        const typename Prec<T>::T2* __restrict__ planes,
+        typename Prec<T>::T2* __restrict__ acc)
+{
+    typedef typename Prec<T>::T2 T2;
+    typedef typename Prec<T>::Rec Rec;
+    const int tile_id = blockIdx.x;
+    const int plane = first_plane + blockIdx.y;
+    uint32_t a, b;
+    es_entry_range(g, keys, tile_start, tile_id, plane, a, b);
+    if (a == b) return;
+    const int tu = tile_id / g.ntile, tv = tile_id % g.ntile;
+    const int gsz = g.grid_size;
+    const int rows_valid = min(ES_TILE, gsz - tu * ES_TILE);
+    const int cols_valid = min(ES_TILE, gsz - tv * ES_TILE);
+    const T2* in = planes + (size_t) blockIdx.y * gsz * gsz +
+            (size_t) (tu * ES_TILE) * gsz + (size_t) (tv * ES_TILE);
+    const int w_sup = g.support;
+    const T beta = (T) g.beta;
+    const T inv_hs = (T) (2.0 / (double) w_sup);
+
+    for (uint32_t e = a + threadIdx.x; e < b; e += ES_GATHER_THREADS)
+    {
+        const Rec r = records[e];
+        const int dp = plane - r.p0;
+        if (dp < 0 || dp > w_sup) continue;
+        const T kw = es_psi(beta, ((T) dp + r.dw) * inv_hs);
+        const int lu0 = r.lu0, lv0 = r.lv0;
+        T kv[NS];
+        #pragma unroll
+        for (int c = 0; c < NS; ++c)
+        {
+            const int col = lv0 + c;
+            const bool ok = (c <= w_sup) && col >= 0 && col < cols_valid;
+            T k = ok ? es_psi(beta, ((T) c + r.dv) * inv_hs) : (T) 0;
+            kv[c] = (col & 1) ? -k : k;
+        }
+        T sum_re = (T) 0, sum_im = (T) 0;
+        for (int s = 0; s <= w_sup; ++s)
+        {
+            const int row = lu0 + s;
+            if (row < 0 || row >= rows_valid) continue;
+            T ku = es_psi(beta, ((T) s + r.du) * inv_hs);
+            if (row & 1) ku = -ku;
+            const T2* prow = in + (size_t) row * gsz + lv0;
+            T row_re = (T) 0, row_im = (T) 0;
+            #pragma unroll
+            for (int c = 0; c < NS; ++c)
+            {
+                if (kv[c] != (T) 0)
+                {
+                    const T2 cell = prow[c];
+                    row_re += cell.x * kv[c];
+                    row_im += cell.y * kv[c];
+                }
+            }
+            sum_re += row_re * ku;
+            sum_im += row_im * ku;
+        }
+        T2 t = acc[e];
+        t.x += sum_re * kw;
+        t.y += sum_im * kw;
+        acc[e] = t;
+    }
+}
+
+template<typename T>
+__global__ void __launch_bounds__(256) es_finish_degrid_kernel(
+        const typename Prec<T>::Rec* __restrict__ records,
+        const typename Prec<T>::T2* __restrict__ acc, int64_t num_entries,
+        T* __restrict__ vis)
+{
+    const int64_t e = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= num_entries) return;
+    const typename Prec<T>::T2 t = acc[e];
+    const size_t idx = records[e].idx;
+    const T flip = records[e].vre;
+    /* kernels.cu:267-268 */
+    atomicAdd(&vis[2 * idx], t.x);
+    atomicAdd(&vis[2 * idx + 1], t.y * flip);
+}
+
+/* ------------------------------------------------------------ w-screen */
+
+/* (cos, sin)(2 pi sign w (n-1)) / n with the phase reduced in fp64:
+ * kernels.cu:110-123. nm1 = n - 1, xn = 1 / n. */
+template<typename T>
+__device__ __forceinline__ void es_phasor(double w, double nm1, double xn,
+        double sign, T& re, T& im);
+
+template<>
+__device__ __forceinline__ void es_phasor<float>(double w, double nm1,
+        double xn, double sign, float& re, float& im)
+{
+    double t = w * nm1;            /* turns */
+    t -= rint(t);
+    float s, c;
+    sincospif((float) (2.0 * sign * t), &s, &c);
+    re = c * (float) xn;
+    im = s * (float) xn;
+}
+
+template<>
+__device__ __forceinline__ void es_phasor<double>(double w, double nm1,
+        double xn, double sign, double& re, double& im)
+{
+    double t = w * nm1;
+    t -= rint(t);
+    double s, c;
+    sincospi(2.0 * sign * t, &s, &c);
+    re = c * xn;
+    im = s * xn;
+}
+
+#define ES_SCREEN_BX 32
+#define ES_SCREEN_BY 8
+
+template<typename T>
+__global__ void __launch_bounds__(ES_SCREEN_BX * ES_SCREEN_BY)
+es_apply_screen_kernel(EsGeom g,
+        const typename Prec<T>::T2* __restrict__ planes, int first_plane,
+        int nplanes, T* __restrict__ dirty)
+{
+    typedef typename Prec<T>::T2 T2;
+    const int i = blockIdx.x * ES_SCREEN_BX + threadIdx.x;
+    const int j = blockIdx.y * ES_SCREEN_BY + threadIdx.y;
+    const int n = g.image_size, half = n / 2, gsz = g.grid_size;
+    if (i > half || j > half) return;
+    const double l = g.pixel_size * (double) i, m = g.pixel_size * (double) j;
+    const double sos = l * l + m * m;
+    const double nm1 = (-sos) / (sqrt(1.0 - sos) + 1.0);
+    const double xn = 1.0 / (nm1 + 1.0);
+    T s_pp = 0, s_pn = 0, s_np = 0, s_nn = 0;
+    const size_t centre = (size_t) (gsz / 2) * gsz + (size_t) (gsz / 2);
+    const ptrdiff_t dj = (ptrdiff_t) j * gsz;
+    for (int q = 0; q < nplanes; ++q)
+    {
+        T cr = (T) 1, ci = (T) 0;
+        if (g.do_wstacking)
+        {
+            const double w = (double) (first_plane + q) * g.inv_w_scale +
+                    g.min_plane_w;
+            es_phasor<T>(w, nm1, xn, -1.0, cr, ci);
+        }
+        const T2* p = planes + (size_t) q * gsz * gsz + centre;
+        /* kernels.cu:487-502 */
+        const T2 a = p[dj + i], b = p[-dj + i], c = p[dj - i], d = p[-dj - i];
+        s_pp += a.x * cr - a.y * ci;
+        s_pn += b.x * cr - b.y * ci;
+        s_np += c.x * cr - c.y * ci;
+        s_nn += d.x * cr - d.y * ci;
+    }
+    if ((i + j) & 1)
+    {
+        s_pp = -s_pp; s_pn = -s_pn; s_np = -s_np; s_nn = -s_nn;
+    }
+    /* kernels.cu:516-545: image offsets -N/2 .. N/2-1 */
+    T* img = dirty + (size_t) half * n + half;
+    const ptrdiff_t ij = (ptrdiff_t) j * n;
+    if (i < half && j < half) img[ij + i] += s_pp;
+    if (i > 0 && j < half) img[ij - i] += s_np;
+    if (j > 0 && i < half) img[-ij + i] += s_pn;
+    if (i > 0 && j > 0) img[-ij - i] += s_nn;
+}
+
+template<typename T>
+__global__ void __launch_bounds__(ES_SCREEN_BX * ES_SCREEN_BY)
+es_reverse_screen_kernel(EsGeom g, const T* __restrict__ dirty,
+        int first_plane, int nplanes,
+        typename Prec<T>::T2* __restrict__ planes)
+{
+    typedef typename Prec<T>::T2 T2;
+    const int i = blockIdx.x * ES_SCREEN_BX + threadIdx.x;
+    const int j = blockIdx.y * ES_SCREEN_BY + threadIdx.y;
+    const int n = g.image_size, half = n / 2, gsz = g.grid_size;
+    if (i > half || j > half) return;
+    const T* img = dirty + (size_t) half * n + half;
+    const ptrdiff_t ij = (ptrdiff_t) j * n;
+    /* kernels.cu:580-613 */
+    const bool w_pp = (i < half && j < half), w_np = (i > 0 && j < half);
+    const bool w_pn = (j > 0 && i < half), w_nn = (i > 0 && j > 0);
+    T d_pp = w_pp ? img[ij + i] : (T) 0;
+    T d_np = w_np ? img[ij - i] : (T) 0;
+    T d_pn = w_pn ? img[-ij + i] : (T) 0;
+    T d_nn = w_nn ? img[-ij - i] : (T) 0;
+    if ((i + j) & 1)
+    {
+        d_pp = -d_pp; d_np = -d_np; d_pn = -d_pn; d_nn = -d_nn;
+    }
+    const double l = g.pixel_size * (double) i, m = g.pixel_size * (double) j;
+    const double sos = l * l + m * m;
+    const double nm1 = (-sos) / (sqrt(1.0 - sos) + 1.0);
+    const double xn = 1.0 / (nm1 + 1.0);
+    const size_t centre = (size_t) (gsz / 2) * gsz + (size_t) (gsz / 2);
+    const ptrdiff_t dj = (ptrdiff_t) j * gsz;
+    for (int q = 0; q < nplanes; ++q)
+    {
+        T cr = (T) 1, ci = (T) 0;
+        if (g.do_wstacking)
+        {
+            const double w = (double) (first_plane + q) * g.inv_w_scale +
+                    g.min_plane_w;
+            es_phasor<T>(w, nm1, xn, 1.0, cr, ci);
+        }
+        T2* p = planes + (size_t) q * gsz * gsz + centre;
+        T2 o;
+        /* kernels.cu:644-676 */
+        if (w_pp) { o.x = cr * d_pp; o.y = ci * d_pp; p[dj + i] = o; }
+        if (w_pn) { o.x = cr * d_pn; o.y = ci * d_pn; p[-dj + i] = o; }
+        if (w_np) { o.x = cr * d_np; o.y = ci * d_np; p[dj - i] = o; }
+        if (w_nn) { o.x = cr * d_nn; o.y = ci * d_nn; p[-dj - i] = o; }
+    }
+}
+
+/* Zero every plane cell the reverse w-screen does not write (the padding
+ * around the image footprint): replaces the per-plane cudaMemset of
+ * es_fft.cpp:840 without touching the footprint twice. */
+template<typename T>
+__global__ void __launch_bounds__(256) es_zero_padding_kernel(EsGeom g,
+        int nplanes, typename Prec<T>::T2* __restrict__ planes)
+{
+    typedef typename Prec<T>::T2 T2;
+    const int gsz = g.grid_size, half = g.image_size / 2;
+    const int row = blockIdx.x;
+    const int col = blockIdx.y * blockDim.x + threadIdx.x;
+    if (col >= gsz) return;
+    const int a = row - gsz / 2, b = col - gsz / 2;
+    const bool inside = (a >= -half && a < half && b >= -half && b < half);
+    if (inside) return;
+    T2 zero; zero.x = (T) 0; zero.y = (T) 0;
+    for (int q = 0; q < nplanes; ++q)
+        planes[(size_t) q * gsz * gsz + (size_t) row * gsz + col] = zero;
+}
+
+/* ---------------------------------------------------------- correction */
+
+/* kernels.cu:690-769 (and conv_corr, :69-87; the quadrature is fp64 in both
+ * precisions there too because PI is a double macro). */
+template<typename T>
+__global__ void __launch_bounds__(ES_SCREEN_BX * ES_SCREEN_BY)
+es_correct_kernel(EsGeom g, T* __restrict__ dirty,
+        const double* __restrict__ qk, const double* __restrict__ qn,
+        const double* __restrict__ qw, const double* __restrict__ cc)
+{
+    const int i = blockIdx.x * ES_SCREEN_BX + threadIdx.x;
+    const int j = blockIdx.y * ES_SCREEN_BY + threadIdx.y;
+    const int n = g.image_size, half = n / 2;
+    if (i > half || j > half) return;
+    const double l = g.pixel_size * (double) i, m = g.pixel_size * (double) j;
+    const double norm2 = g.conv_corr_norm_factor * g.conv_corr_norm_factor;
+    double correction = cc[i] * cc[j];
+    if (g.do_wstacking)
+    {
+        const double nn = sqrt(1.0 - l * l - m * m) - 1.0;
+        const double k = nn * g.inv_w_scale;
+        const double support = (double) g.support;
+        const int p = (int) ceil(1.5 * support + 2.0);
+        double sum = 0.0;
+        for (int q = 0; q < p; ++q)
+            sum += qk[q] * cos(ES_PI * k * support * qn[q]) * qw[q];
+        correction *= (sum * support) * norm2;
+    }
+    else
+    {
+        correction *= norm2;
+    }
+    const T scale = (T) (1.0 / correction);
+    T* img = dirty + (size_t) half * n + half;
+    const ptrdiff_t ij = (ptrdiff_t) j * n;
+    if (i < half && j < half) img[ij + i] *= scale;
+    if (i > 0 && j < half) img[ij - i] *= scale;
+    if (j > 0 && i < half) img[-ij + i] *= scale;
+    if (i > 0 && j > 0) img[-ij - i] *= scale;
+}
+
+inline unsigned int blocks_for(int64_t n, int threads)
+{
+    return (unsigned int) ((n + threads - 1) / threads);
+}
+
+template<typename T, int CS>
+static int launch_scatter_t(const EsGeom* g, const void* records,
+        const uint64_t* keys, const uint32_t* tile_start, int first_plane,
+        int nplanes, void* planes, cudaStream_t s)
+{
+    typedef typename Prec<T>::T2 T2;
+    typedef typename Prec<T>::Rec Rec;
+    const size_t smem = (size_t) ES_TILE * ES_TILE * sizeof(T2);
+    static bool configured = false;
+    if (!configured)
+    {
+        cudaError_t err = cudaFuncSetAttribute(es_scatter_kernel<T, CS>,
+                cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
+        if (err != cudaSuccess) return (int) err;
+        configured = true;
+    }
+    dim3 grid((unsigned) (g->ntile * g->ntile), (unsigned) nplanes);
+    es_scatter_kernel<T, CS><<<grid, ES_SCATTER_THREADS, smem, s>>>(*g,
+            (const Rec*) records, keys, tile_start, first_plane, (T2*) planes);
+    return (int) cudaGetLastError();
+}
+
+template<typename T>
+static int launch_gather_t(const EsGeom* g, const void* records,
+        const uint64_t* keys, const uint32_t* tile_start, int first_plane,
+        int nplanes, const void* planes, void* acc, cudaStream_t s)
+{
+    typedef typename Prec<T>::T2 T2;
+    typedef typename Prec<T>::Rec Rec;
+    dim3 grid((unsigned) (g->ntile * g->ntile), (unsigned) nplanes);
+    if (g->support + 1 <= 9)
+        es_gather_kernel<T, 9><<<grid, ES_GATHER_THREADS, 0, s>>>(*g,
+                (const Rec*) records, keys, tile_start, first_plane,
+                (const T2*) planes, (T2*) acc);
+    else
+        es_gather_kernel<T, 17><<<grid, ES_GATHER_THREADS, 0, s>>>(*g,
+                (const Rec*) records, keys, tile_start, first_plane,
+                (const T2*) planes, (T2*) acc);
+    return (int) cudaGetLastError();
+}
+
+} // namespace
+
+/* ================================================================ C ABI */
+
+extern "C" {
+
+size_t es_record_bytes(int is_double)
+{
+    return is_double ? sizeof(EsRecD) : sizeof(EsRecF);
+}
+
+int es_launch_count_entries(const EsGeom* g, const void* uvw, const void* freq,
+        uint8_t* counts, es_stream_t stream)
+{
+    const int64_t nvis = (int64_t) g->num_rows * g->num_chan;
+    if (nvis == 0) return 0;
+    cudaStream_t s = (cudaStream_t) stream;
+    if (g->is_double)
+        es_count_entries_kernel<double><<<blocks_for(nvis, 256), 256, 0, s>>>(
+                *g, (const double*) uvw, (const double*) freq, counts);
+    else
+        es_count_entries_kernel<float><<<blocks_for(nvis, 256), 256, 0, s>>>(
+                *g, (const float*) uvw, (const float*) freq, counts);
+    return (int) cudaGetLastError();
+}
+
+int es_scan_counts(const uint8_t* counts, uint32_t* offsets, int64_t n,
+        void* temp, size_t* temp_bytes, es_stream_t stream)
+{
+    cub::TransformInputIterator<uint32_t, CastU8, const uint8_t*> in(counts,
+            CastU8());
+    return (int) cub::DeviceScan::ExclusiveSum(temp, *temp_bytes, in, offsets,
+            n, (cudaStream_t) stream);
+}
+
+int es_launch_emit_entries(const EsGeom* g, const void* uvw, const void* freq,
+        const uint32_t* offsets, uint64_t* keys, uint32_t* vals,
+        es_stream_t stream)
+{
+    const int64_t nvis = (int64_t) g->num_rows * g->num_chan;
+    if (nvis == 0) return 0;
+    cudaStream_t s = (cudaStream_t) stream;
+    if (g->is_double)
+        es_emit_entries_kernel<double><<<blocks_for(nvis, 256), 256, 0, s>>>(
+                *g, (const double*) uvw, (const double*) freq, offsets, keys,
+                vals);
+    else
+        es_emit_entries_kernel<float><<<blocks_for(nvis, 256), 256, 0, s>>>(
+                *g, (const float*) uvw, (const float*) freq, offsets, keys,
+                vals);
+    return (int) cudaGetLastError();
+}
+
+int es_sort_entries(const uint64_t* keys_in, uint64_t* keys_out,
+        const uint32_t* vals_in, uint32_t* vals_out, int64_t num_entries,
+        int end_bit, void* temp, size_t* temp_bytes, es_stream_t stream)
+{
+    return (int) cub::DeviceRadixSort::SortPairs(temp, *temp_bytes, keys_in,
+            keys_out, vals_in, vals_out, num_entries, 0, end_bit,
+            (cudaStream_t) stream);
+}
+
+int es_launch_tile_bounds(const EsGeom* g, const uint64_t* keys,
+        int64_t num_entries, uint32_t* tile_start, es_stream_t stream)
+{
+    cudaStream_t s = (cudaStream_t) stream;
+    const size_t ntiles = (size_t) g->ntile * g->ntile;
+    if (num_entries == 0)
+        return (int) cudaMemsetAsync(tile_start, 0,
+                (ntiles + 1) * sizeof(uint32_t), s);
+    es_tile_bounds_kernel<<<blocks_for(num_entries, 256), 256, 0, s>>>(*g,
+            keys, num_entries, tile_start);
+    return (int) cudaGetLastError();
+}
+
+int es_launch_build_records(const EsGeom* g, const void* uvw, const void* freq,
+        const void* vis, const void* weight, const uint64_t* keys,
+        const uint32_t* vals, int64_t num_entries, void* records,
+        es_stream_t stream)
+{
+    if (num_entries == 0) return 0;
+    cudaStream_t s = (cudaStream_t) stream;
+    if (g->is_double)
+        es_build_records_kernel<double><<<blocks_for(num_entries, 256), 256, 0,
+                s>>>(*g, (const double*) uvw, (const double*) freq,
+                (const double2*) vis, (const double*) weight, keys, vals,
+                num_entries, (EsRecD*) records);
+    else
+        es_build_records_kernel<float><<<blocks_for(num_entries, 256), 256, 0,
+                s>>>(*g, (const float*) uvw, (const float*) freq,
+                (const float2*) vis, (const float*) weight, keys, vals,
+                num_entries, (EsRecF*) records);
+    return (int) cudaGetLastError();
+}
+
+int es_launch_scatter(const EsGeom* g, const void* records,
+        const uint64_t* keys, const uint32_t* tile_start, int first_plane,
+        int nplanes, void* planes, es_stream_t stream)
+{
+    cudaStream_t s = (cudaStream_t) stream;
+    const bool wide = g->support + 1 > 16;
+    if (g->is_double)
+        return wide ?
+            launch_scatter_t<double, 32>(g, records, keys, tile_start,
+                    first_plane, nplanes, planes, s) :
+            launch_scatter_t<double, 16>(g, records, keys, tile_start,
+                    first_plane, nplanes, planes, s);
+    return wide ?
+        launch_scatter_t<float, 32>(g, records, keys, tile_start, first_plane,
+                nplanes, planes, s) :
+        launch_scatter_t<float, 16>(g, records, keys, tile_start, first_plane,
+                nplanes, planes, s);
+}
+
+int es_launch_apply_screen(const EsGeom* g, const void* planes,
+        int first_plane, int nplanes, void* dirty, es_stream_t stream)
+{
+    cudaStream_t s = (cudaStream_t) stream;
+    const int half = g->image_size / 2;
+    dim3 block(ES_SCREEN_BX, ES_SCREEN_BY);
+    dim3 grid(blocks_for(half + 1, ES_SCREEN_BX), blocks_for(half + 1, ES_SCREEN_BY));
+    if (g->is_double)
+        es_apply_screen_kernel<double><<<grid, block, 0, s>>>(*g,
+                (const double2*) planes, first_plane, nplanes, (double*) dirty);
+    else
+        es_apply_screen_kernel<float><<<grid, block, 0, s>>>(*g,
+                (const float2*) planes, first_plane, nplanes, (float*) dirty);
+    return (int) cudaGetLastError();
+}
+
+int es_launch_reverse_screen(const EsGeom* g, const void* dirty,
+        int first_plane, int nplanes, void* planes, es_stream_t stream)
+{
+    cudaStream_t s = (cudaStream_t) stream;
+    const int half = g->image_size / 2;
+    dim3 zgrid((unsigned) g->grid_size, blocks_for(g->grid_size, 256));
+    dim3 block(ES_SCREEN_BX, ES_SCREEN_BY);
+    dim3 grid(blocks_for(half + 1, ES_SCREEN_BX), blocks_for(half + 1, ES_SCREEN_BY));
+    if (g->is_double)
+    {
+        es_zero_padding_kernel<double><<<zgrid, 256, 0, s>>>(*g, nplanes,
+                (double2*) planes);
+        es_reverse_screen_kernel<double><<<grid, block, 0, s>>>(*g,
+                (const double*) dirty, first_plane, nplanes, (double2*) planes);
+    }
+    else
+    {
+        es_zero_padding_kernel<float><<<zgrid, 256, 0, s>>>(*g, nplanes,
+                (float2*) planes);
+        es_reverse_screen_kernel<float><<<grid, block, 0, s>>>(*g,
+                (const float*) dirty, first_plane, nplanes, (float2*) planes);
+    }
+    return (int) cudaGetLastError();
+}
+
+int es_launch_gather(const EsGeom* g, const void* records,
+        const uint64_t* keys, const uint32_t* tile_start, int first_plane,
+        int nplanes, const void* planes, void* acc, es_stream_t stream)
+{
+    cudaStream_t s = (cudaStream_t) stream;
+    return g->is_double ?
+        launch_gather_t<double>(g, records, keys, tile_start, first_plane,
+                nplanes, planes, acc, s) :
+        launch_gather_t<float>(g, records, keys, tile_start, first_plane,
+                nplanes, planes, acc, s);
+}
+
+int es_launch_finish_degrid(const EsGeom* g, const void* records,
+        const void* acc, int64_t num_entries, void* vis, es_stream_t stream)
+{
+    if (num_entries == 0) return 0;
+    cudaStream_t s = (cudaStream_t) stream;
+    if (g->is_double)
+        es_finish_degrid_kernel<double><<<blocks_for(num_entries, 256), 256, 0,
+                s>>>((const EsRecD*) records, (const double2*) acc,
+                num_entries, (double*) vis);
+    else
+        es_finish_degrid_kernel<float><<<blocks_for(num_entries, 256), 256, 0,
+                s>>>((const EsRecF*) records, (const float2*) acc,
+                num_entries, (float*) vis);
+    return (int) cudaGetLastError();
+}
+
+int es_launch_correct(const EsGeom* g, void* dirty, const double* quad_kernel,
+        const double* quad_nodes, const double* quad_weights,
+        const double* conv_corr, es_stream_t stream)
+{
+    cudaStream_t s = (cudaStream_t) stream;
+    const int half = g->image_size / 2;
+    dim3 block(ES_SCREEN_BX, ES_SCREEN_BY);
+    dim3 grid(blocks_for(half + 1, ES_SCREEN_BX), blocks_for(half + 1, ES_SCREEN_BY));
+    if (g->is_double)
+        es_correct_kernel<double><<<grid, block, 0, s>>>(*g, (double*) dirty,
+                quad_kernel, quad_nodes, quad_weights, conv_corr);
+    else
+        es_correct_kernel<float><<<grid, block, 0, s>>>(*g, (float*) dirty,
+                quad_kernel, quad_nodes, quad_weights, conv_corr);
+    return (int) cudaGetLastError();
+}
+
+int es_launch_plane_histogram(const EsGeom* g, const void* uvw,
+        const void* freq, unsigned long long* hist, es_stream_t stream)
+{
+    const int64_t nvis = (int64_t) g->num_rows * g->num_chan;
+    if (nvis == 0) return 0;
+    cudaStream_t s = (cudaStream_t) stream;
+    if (g->is_double)
+        es_plane_histogram_kernel<double><<<blocks_for(nvis, 256), 256, 0, s>>>(
+                *g, (const double*) uvw, (const double*) freq, hist);
+    else
+        es_plane_histogram_kernel<float><<<blocks_for(nvis, 256), 256, 0, s>>>(
+                *g, (const float*) uvw, (const float*) freq, hist);
+    return (int) cudaGetLastError();
+}
+
+} // extern "C"

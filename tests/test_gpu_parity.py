@@ -1,0 +1,210 @@
+"""Parity of the CUDA path with the oracle, through the C-ABI, on a B200.
+
+Tolerance (BASELINE.json north_star): max|err| / max|ref| <= 1e-5 for fp32
+configurations, <= 1e-10 for fp64, against the oracle (= the reference
+algorithm and plan with fp64 coordinates, oracle/es_oracle.*, pinned to the
+reference's own kernel source in tests/test_oracle.py).
+"""
+import os
+
+import numpy as np
+import pytest
+
+from tests import synth
+from tests.helpers import (TOL, check_parity, product_degrid, product_grid,
+                           rel_max)
+
+pytestmark = pytest.mark.gpu
+
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden", "golden_cases.npz")
+
+
+def load_golden(name):
+    z = np.load(GOLDEN)
+    return {k.split("/", 1)[1]: z[k] for k in z.files if k.startswith(name + "/")}
+
+
+def golden_case(name, single=False):
+    g = load_golden(name)
+    case = dict(uvw=g["uvw"], freq_hz=g["freq"], vis=g["vis"],
+                weight=g["weight"], image=g["image"],
+                pixel_size=float(g["pix"]))
+    if single:
+        case = synth._cast(case, True)  # pylint: disable=protected-access
+    return g, case
+
+
+@pytest.mark.parametrize("name", ["f64_3d", "f64_2d", "f64_w14"])
+def test_golden_vectors_fp64(name):
+    """Committed outputs of the reference's own kernels (host build)."""
+    g, case = golden_case(name)
+    dirty, gridder = product_grid(case, float(g["eps"]), bool(g["wstack"]))
+    info = gridder.info()
+    assert info["grid_size"] == int(g["grid_size"])
+    assert info["support"] == int(g["support"])
+    assert info["num_total_w_grids"] == int(g["planes"])
+    vis, img, _ = product_degrid(case, float(g["eps"]), bool(g["wstack"]), gridder)
+    assert rel_max(dirty, g["dirty"]) <= 1e-10
+    assert rel_max(vis, g["pred"]) <= 1e-10
+    assert rel_max(img, g["image_corrected"]) <= 1e-10
+
+
+def test_golden_vectors_fp32_three_way():
+    """fp32: new-vs-oracle64 must meet 1e-5; the reference's literal fp32
+    arithmetic (ref32) is reported beside it."""
+    g, case = golden_case("f32plan_f64", single=True)
+    dirty, gridder = product_grid(case, float(g["eps"]), True)
+    vis, _, _ = product_degrid(case, float(g["eps"]), True, gridder)
+    new_vs_oracle = (rel_max(dirty, g["dirty"]), rel_max(vis, g["pred"]))
+    ref32_vs_oracle = (rel_max(g["dirty_ref32"], g["dirty"]),
+                       rel_max(g["pred_ref32"], g["pred"]))
+    new_vs_ref32 = (rel_max(dirty, g["dirty_ref32"]),
+                    rel_max(vis, g["pred_ref32"]))
+    print("new-vs-oracle64", new_vs_oracle, "ref32-vs-oracle64",
+          ref32_vs_oracle, "new-vs-ref32", new_vs_ref32)
+    assert max(new_vs_oracle) <= 1e-5
+
+
+@pytest.mark.parametrize("wstack,eps", [(True, 1e-5), (False, 1e-5), (True, 1e-12)])
+def test_c1_reference_test_generator_fp64(wstack, eps):
+    """BASELINE config C1: 1000 x 10, 256^2, fp64, grid + degrid."""
+    check_parity(synth.reference_test_case(256), eps, wstack)
+
+
+@pytest.mark.parametrize("wstack", [True, False])
+def test_c1_reference_test_generator_fp32(wstack):
+    check_parity(synth.reference_test_case(256, single=True), 1e-5, wstack)
+
+
+def test_support_16_fallback_path():
+    """Unattainable epsilon selects W=16 (17-tap footprints: the wide lane
+    mapping of the scatter kernel and the 17-slot gather)."""
+    case = synth.reference_test_case(128, num_vis=300, num_chan=4)
+    check_parity(case, 1e-30, True)
+
+
+@pytest.mark.parametrize("single,wstack,eps", [
+    (True, False, 1e-5), (True, True, 1e-5), (False, False, 1e-12),
+    (False, True, 1e-12)])
+def test_adjointness_reference_criterion(single, wstack, eps):
+    """The reference's own test (test_gridder_uvw_es_fft.py:500-529,532-637):
+    1000 x 10 visibilities, 1024^2 image, thresholds 1e-5 / 1e-12."""
+    c = synth.reference_test_case(1024, single=single)
+    dirty, gridder = product_grid(c, eps, wstack)
+    vis, _, _ = product_degrid(c, eps, wstack, gridder)
+    adj1 = np.vdot(dirty.astype(np.float64), c["image"].astype(np.float64))
+    adj2 = np.vdot(vis.astype(np.complex128), c["vis"].astype(np.complex128)).real
+    err = abs(adj1 - adj2) / max(abs(adj1), abs(adj2))
+    print("adjointness", adj1, adj2, err)
+    assert err < (1e-5 if single else 1e-12)
+
+
+def test_c2_uniform_box_scaled_fp32():
+    """BASELINE config C2 geometry at 1/4 linear size (1024^2, 250 x 256)."""
+    case = synth.uniform_box(250, 256, 1024, single=True)
+    check_parity(case, 1e-5, True)
+
+
+def test_c3_mid_like_predict_scaled_fp64():
+    """BASELINE config C3 geometry scaled down: fp64, eps=1e-10, degridding."""
+    case = synth.mid_like_predict(24, 1, 32, 512, single=False, r_max=3e3)
+    check_parity(case, 1e-10, True, do_grid=False)
+
+
+def test_c4_ska_low_scaled_fp32():
+    """BASELINE config C4 geometry scaled down (64 stations, 32 channels,
+    1024^2): core-heavy layout -> very uneven tile occupancy."""
+    case = synth.ska_low_snapshot(64, 32, 1024, single=True, r_max=4e3)
+    check_parity(case, 1e-5, True)
+
+
+def test_c5_wide_field_scaled_fp32():
+    """BASELINE config C5 geometry scaled down: eps=1e-4 (W=7, odd support),
+    20 degree field, many w-planes; grid -> degrid adjoint pair."""
+    case = synth.wide_field(400, 16, 512, max_w_lambda=600.0, single=True)
+    out = check_parity(case, 1e-4, True)
+    print(out)
+
+
+def test_edge_cases_clipping_origin_and_offgrid():
+    """Footprints clipped at the grid edge (not wrapped), a visibility exactly
+    on a grid point (W+1 taps), visibilities entirely off the grid, w < 0
+    (conjugate flip), zero weights."""
+    c = synth.reference_test_case(128, num_vis=64, num_chan=3)
+    pix, f0 = c["pixel_size"], c["freq_hz"][0]
+    lam_cells = 1.0 / (pix * f0 / synth.C_0)  # metres per uv-plane extent
+    c["uvw"][0] = 0.0                          # exactly on the origin cell
+    c["uvw"][1] = [0.4999 * lam_cells, -0.4999 * lam_cells, 3.0]   # grid corner
+    c["uvw"][2] = [3.0 * lam_cells, 0.0, 1.0]                      # off grid
+    c["uvw"][3, 2] = -abs(c["uvw"][3, 2]) - 1.0                    # flipped
+    c["weight"][4] = 0.0
+    check_parity(c, 1e-7, True)
+    check_parity(c, 1e-7, False)
+
+
+def test_single_visibility_and_single_channel():
+    c = synth.reference_test_case(64, num_vis=1, num_chan=1)
+    c["uvw"][0] = [13.7, -4.2, 9.1]
+    check_parity(c, 1e-6, True)
+
+
+def test_gridding_accumulates_and_degridding_adds():
+    """Side effects that are part of the contract."""
+    c = synth.reference_test_case(128, num_vis=100, num_chan=4)
+    d0, gridder = product_grid(c, 1e-6, True)
+    base = np.full_like(d0, 0.25)
+    d1 = base.copy()
+    gridder.grid_uvw_es_fft(c["uvw"], c["freq_hz"], c["vis"], c["weight"], d1)
+    ones = np.ones_like(d0)
+    corr = ones.copy()
+    gridder.correct_image(corr)          # correction factors
+    assert rel_max(d1, d0 + 0.25 * corr) <= 1e-12
+    v0, img0, _ = product_degrid(c, 1e-6, True, gridder)
+    start = np.full(v0.shape, 1.0 - 2.0j)
+    v1 = start.copy()
+    img1 = c["image"].copy()
+    gridder.ifft_grid_uvw_es(c["uvw"], c["freq_hz"], v1, c["weight"] * 0.0, img1)
+    assert rel_max(v1, v0 + start) <= 1e-12      # += and weight ignored
+    assert np.array_equal(img0, img1)            # corrected in place, same way
+    assert not np.array_equal(img1, c["image"])
+
+
+def test_results_are_deterministic():
+    """No atomics in the scatter path: two runs are bitwise identical."""
+    c = synth.ska_low_snapshot(48, 16, 512, single=True, r_max=2e3)
+    d0, gridder = product_grid(c, 1e-5, True)
+    d1, _ = product_grid(c, 1e-5, True, gridder)
+    assert np.array_equal(d0, d1)
+
+
+def test_plane_partition_sums_to_full_result():
+    """Multi-GPU decomposition on one device: partial dirty images over
+    disjoint w-plane ranges sum to the full image; partial predictions add."""
+    c = synth.reference_test_case(256, num_vis=400, num_chan=8)
+    full, gridder = product_grid(c, 1e-6, True)
+    planes = gridder.info()["num_total_w_grids"]
+    hist = gridder.plane_histogram(c["uvw"], c["freq_hz"])
+    assert hist.shape == (planes,) and hist.sum() > 0
+    cut = planes // 3
+    parts = []
+    for lo, hi in ((0, cut), (cut, planes)):
+        gridder.set_plane_range(lo, hi, apply_correction=False)
+        part, _ = product_grid(c, 1e-6, True, gridder)
+        parts.append(part)
+    total = parts[0] + parts[1]
+    gridder.correct_image(total)
+    assert rel_max(total, full) <= 1e-13
+    gridder.set_plane_range(0, planes, True)
+    v_full, _, _ = product_degrid(c, 1e-6, True, gridder)
+    img = c["image"].copy()
+    gridder.correct_image(img)
+    v_sum = np.zeros_like(v_full)
+    for lo, hi in ((0, cut), (cut, planes)):
+        gridder.set_plane_range(lo, hi, apply_correction=False)
+        tmp = img.copy()
+        gridder.ifft_grid_uvw_es(c["uvw"], c["freq_hz"], v_sum, c["weight"], tmp)
+    assert rel_max(v_sum, v_full) <= 1e-13
+
+
+def test_parity_tolerances_are_the_stated_ones():
+    assert TOL[np.dtype(np.float32)] == 1e-5 and TOL[np.dtype(np.float64)] == 1e-10
