@@ -179,7 +179,14 @@ def make_plan(image_size, pixel_size, epsilon, do_w_stacking, min_abs_w,
             nmin = -math.sqrt(abs(1.0 - s)) - 1.0
         w_scale = 0.25 / abs(nmin)
         nw = int((max_abs_w - min_abs_w) / w_scale + 2)  # C truncation
-        w_scale = 1.0 / ((1.0 + 1e-13) * (max_abs_w - min_abs_w) / (nw - 1))
+        if max_abs_w > min_abs_w:
+            w_scale = 1.0 / ((1.0 + 1e-13) * (max_abs_w - min_abs_w) / (nw - 1))
+        else:
+            # A single |w| value divides by zero in the reference
+            # (es_fft.cpp:358, undefined there). The drop-in keeps the
+            # unstretched plane spacing; the oracle defines the same.
+            nw = 2
+            w_scale = 1.0 / w_scale
         plan.update(
             min_abs_w=min_abs_w, max_abs_w=max_abs_w, w_scale=w_scale,
             min_plane_w=min_abs_w - (0.5 * support - 1.0) / w_scale,

@@ -70,6 +70,9 @@ struct sdp_GridderUvwEsFft
     int32_t timing;
     cudaEvent_t ev[8];
     int32_t have_events;
+    int32_t stats_pending; /* 1 grid / 2 degrid timings not yet collected */
+    cudaEvent_t* stage_ev; /* 4 per plane batch when timing is enabled */
+    int32_t stage_cap, stage_used;
 };
 
 /* ------------------------------------------------------------ utilities */
@@ -312,6 +315,9 @@ void sdp_gridder_uvw_es_fft_free_plan(sdp_GridderUvwEsFft* plan)
         buffer_free(all[k]);
     if (plan->have_events)
         for (int k = 0; k < 8; ++k) (void) cudaEventDestroy(plan->ev[k]);
+    for (int k = 0; k < plan->stage_cap; ++k)
+        (void) cudaEventDestroy(plan->stage_ev[k]);
+    free(plan->stage_ev);
     free(plan);
 }
 
@@ -498,16 +504,36 @@ void sdp_gridder_uvw_es_fft_set_plane_range(sdp_GridderUvwEsFft* plan,
     plan->apply_correction = apply_correction;
 }
 
+static double event_ms(sdp_GridderUvwEsFft* plan, int from, int to);
+static void stage_collect(sdp_GridderUvwEsFft* plan, int degrid);
+
 void sdp_gridder_uvw_es_fft_enable_timing(sdp_GridderUvwEsFft* plan,
         int32_t enable)
 {
     if (plan) plan->timing = enable;
 }
 
-void sdp_gridder_uvw_es_fft_get_stats(const sdp_GridderUvwEsFft* plan,
+void sdp_gridder_uvw_es_fft_get_stats(const sdp_GridderUvwEsFft* plan_,
         sdp_EsCallStats* stats)
 {
-    if (plan && stats) *stats = plan->stats;
+    sdp_GridderUvwEsFft* plan = (sdp_GridderUvwEsFft*) plan_;
+    if (!plan || !stats) return;
+    if (plan->stats_pending && plan->timing && plan->have_events)
+    {
+        /* waits for the call whose timings are wanted, nothing else does */
+        if (cudaEventSynchronize(plan->ev[3]) == cudaSuccess)
+        {
+            plan->stats.ms_presort = event_ms(plan, 0, 1);
+            plan->stats.ms_total = event_ms(plan, 0, 3);
+            stage_collect(plan, plan->stats_pending == 2);
+        }
+        else
+        {
+            (void) cudaGetLastError();
+        }
+    }
+    plan->stats_pending = 0;
+    *stats = plan->stats;
 }
 
 /* ----------------------------------------------------------------- FFT */
@@ -774,6 +800,7 @@ static void events_begin(sdp_GridderUvwEsFft* plan)
     memset(&plan->stats, 0, sizeof(plan->stats));
     plan->stats.plane_batch = plan->plane_batch;
     plan->stats.timing_enabled = plan->timing;
+    plan->stage_used = 0;
     if (plan->timing && !plan->have_events)
     {
         int ok = 1;
@@ -784,6 +811,52 @@ static void events_begin(sdp_GridderUvwEsFft* plan)
     }
     if (plan->timing && plan->have_events)
         (void) cudaEventRecord(plan->ev[0], plan->stream);
+}
+
+/* Per-stage timing: four events per plane batch (before stage 1, after
+ * stages 1, 2, 3), summed after the call has drained. */
+static void stage_mark(sdp_GridderUvwEsFft* plan)
+{
+    if (!plan->timing) return;
+    if (plan->stage_used == plan->stage_cap)
+    {
+        const int cap = plan->stage_cap ? 2 * plan->stage_cap : 256;
+        cudaEvent_t* grown = (cudaEvent_t*) realloc(plan->stage_ev,
+                sizeof(cudaEvent_t) * (size_t) cap);
+        if (!grown) return;
+        plan->stage_ev = grown;
+        for (int k = plan->stage_cap; k < cap; ++k)
+        {
+            if (cudaEventCreate(&plan->stage_ev[k]) != cudaSuccess)
+            {
+                (void) cudaGetLastError();
+                plan->stage_cap = k;
+                return;
+            }
+        }
+        plan->stage_cap = cap;
+    }
+    (void) cudaEventRecord(plan->stage_ev[plan->stage_used++], plan->stream);
+}
+
+/* stage order: grid = scatter, fft, screen; degrid = screen, fft, gather */
+static void stage_collect(sdp_GridderUvwEsFft* plan, int degrid)
+{
+    double sum[3] = {0.0, 0.0, 0.0};
+    for (int k = 0; k + 3 < plan->stage_used; k += 4)
+    {
+        for (int j = 0; j < 3; ++j)
+        {
+            float ms = 0.0f;
+            if (cudaEventElapsedTime(&ms, plan->stage_ev[k + j],
+                    plan->stage_ev[k + j + 1]) != cudaSuccess)
+                (void) cudaGetLastError();
+            sum[j] += (double) ms;
+        }
+    }
+    plan->stats.ms_scatter_gather = degrid ? sum[2] : sum[0];
+    plan->stats.ms_fft = sum[1];
+    plan->stats.ms_screen = degrid ? sum[0] : sum[2];
 }
 
 static void event_mark(sdp_GridderUvwEsFft* plan, int k)
@@ -835,14 +908,18 @@ void sdp_grid_uvw_es_fft(sdp_GridderUvwEsFft* plan, const sdp_Mem* uvw,
     {
         int nb = g->plane_end - first;
         if (nb > plan->plane_batch) nb = plan->plane_batch;
+        stage_mark(plan);
         ES_CUDA(es_launch_scatter(g, plan->records.ptr,
                 (const uint64_t*) plan->keys_b.ptr,
                 (const uint32_t*) plan->tile_start.ptr, first, nb,
                 plan->planes.ptr, s));
+        stage_mark(plan);
         fft_exec(plan, nb, 0, status); /* CUFFT_INVERSE, es_fft.cpp:568 */
         if (*status) return;
+        stage_mark(plan);
         ES_CUDA(es_launch_apply_screen(g, plan->planes.ptr, first, nb,
                 a.dirty, s));
+        stage_mark(plan);
         plan->stats.kernel_launches += 2;
         plan->stats.planes_processed += nb;
     }
@@ -860,12 +937,7 @@ void sdp_grid_uvw_es_fft(sdp_GridderUvwEsFft* plan, const sdp_Mem* uvw,
         ES_CUDA(cudaStreamSynchronize(s));
     }
     event_mark(plan, 3);
-    if (plan->timing && plan->have_events)
-    {
-        ES_CUDA(cudaEventSynchronize(plan->ev[3]));
-        plan->stats.ms_presort = event_ms(plan, 0, 1);
-        plan->stats.ms_total = event_ms(plan, 0, 3);
-    }
+    plan->stats_pending = 1; /* timings are collected by get_stats */
 }
 
 /* ----------------------------------------------------------- degridding */
@@ -915,14 +987,18 @@ void sdp_ifft_degrid_uvw_es(sdp_GridderUvwEsFft* plan, const sdp_Mem* uvw,
     {
         int nb = g->plane_end - first;
         if (nb > plan->plane_batch) nb = plan->plane_batch;
+        stage_mark(plan);
         ES_CUDA(es_launch_reverse_screen(g, a.dirty, first, nb,
                 plan->planes.ptr, s));
+        stage_mark(plan);
         fft_exec(plan, nb, 1, status); /* CUFFT_FORWARD, es_fft.cpp:782 */
         if (*status) return;
+        stage_mark(plan);
         ES_CUDA(es_launch_gather(g, plan->records.ptr,
                 (const uint64_t*) plan->keys_b.ptr,
                 (const uint32_t*) plan->tile_start.ptr, first, nb,
                 plan->planes.ptr, plan->acc.ptr, s));
+        stage_mark(plan);
         plan->stats.kernel_launches += 3;
         plan->stats.planes_processed += nb;
     }
@@ -937,12 +1013,7 @@ void sdp_ifft_degrid_uvw_es(sdp_GridderUvwEsFft* plan, const sdp_Mem* uvw,
         ES_CUDA(cudaStreamSynchronize(s));
     }
     event_mark(plan, 3);
-    if (plan->timing && plan->have_events)
-    {
-        ES_CUDA(cudaEventSynchronize(plan->ev[3]));
-        plan->stats.ms_presort = event_ms(plan, 0, 1);
-        plan->stats.ms_total = event_ms(plan, 0, 3);
-    }
+    plan->stats_pending = 2;
 }
 
 /* ----------------------------------------------------------- extensions */

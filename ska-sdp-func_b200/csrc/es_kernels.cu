@@ -264,12 +264,13 @@ __global__ void __launch_bounds__(256) es_plane_histogram_kernel(EsGeom g,
     atomicAdd(&hist[f.p_lo], 1ULL);
 }
 
-/* Range of sorted entries of `tile_id` that can touch `plane`: first owned
- * plane in [plane - W, plane]. Every thread computes it (broadcast loads). */
+/* Range of sorted entries of `tile_id` that can touch a plane in
+ * [plane_first, plane_last]: first owned plane in [plane_first - W,
+ * plane_last]. Every thread computes it (broadcast loads). */
 __device__ __forceinline__ void es_entry_range(const EsGeom& g,
         const uint64_t* __restrict__ keys,
-        const uint32_t* __restrict__ tile_start, int tile_id, int plane,
-        uint32_t& a, uint32_t& b)
+        const uint32_t* __restrict__ tile_start, int tile_id, int plane_first,
+        int plane_last, uint32_t& a, uint32_t& b)
 {
     uint32_t lo = tile_start[tile_id];
     const uint32_t hi = tile_start[tile_id + 1];
@@ -277,8 +278,8 @@ __device__ __forceinline__ void es_entry_range(const EsGeom& g,
     if (lo == hi) return;
     const uint64_t pk = (uint64_t) (g.plane_end - g.plane_begin);
     const uint64_t base = (uint64_t) tile_id * pk;
-    const int kp_hi = plane - g.plane_begin;
-    const int kp_lo = max(kp_hi - g.support, 0);
+    const int kp_hi = plane_last - g.plane_begin;
+    const int kp_lo = max(plane_first - g.plane_begin - g.support, 0);
     const uint64_t key_lo = base + (uint64_t) kp_lo;
     const uint64_t key_hi = base + (uint64_t) kp_hi; /* inclusive */
     uint32_t l = lo, h = hi;
@@ -330,7 +331,7 @@ __global__ void __launch_bounds__(ES_SCATTER_THREADS) es_scatter_kernel(
             (size_t) (tu * ES_TILE) * gsz + (size_t) (tv * ES_TILE);
 
     uint32_t a, b;
-    es_entry_range(g, keys, tile_start, tile_id, plane, a, b);
+    es_entry_range(g, keys, tile_start, tile_id, plane, plane, a, b);
 
     /* 16-byte vectors of the tile rows: VEC cells each. */
     constexpr int VEC = 16 / (int) sizeof(T2);
@@ -428,28 +429,33 @@ __global__ void __launch_bounds__(ES_SCATTER_THREADS) es_scatter_kernel(
 
 #define ES_GATHER_THREADS 128
 
-/* NS: footprint slots per axis handled (support + 1 <= NS). */
+/* One CTA per uv tile, one thread per record, all planes of the resident
+ * batch: a record is read once per batch, its u and v weights are evaluated
+ * once, and its accumulator gets one read-modify-write (owned by exactly one
+ * thread, so no atomics and a deterministic sum).
+ * NS: footprint slots per axis handled (support + 1 <= NS). */
 template<typename T, int NS>
 __global__ void __launch_bounds__(ES_GATHER_THREADS) es_gather_kernel(
         EsGeom g, const typename Prec<T>::Rec* __restrict__ records,
         const uint64_t* __restrict__ keys,
-        const uint32_t* __restrict__ tile_start, int first_plane,
+        const uint32_t* __restrict__ tile_start, int first_plane, int nplanes,
         const typename Prec<T>::T2* __restrict__ planes,
         typename Prec<T>::T2* __restrict__ acc)
 {
     typedef typename Prec<T>::T2 T2;
     typedef typename Prec<T>::Rec Rec;
     const int tile_id = blockIdx.x;
-    const int plane = first_plane + blockIdx.y;
     uint32_t a, b;
-    es_entry_range(g, keys, tile_start, tile_id, plane, a, b);
+    es_entry_range(g, keys, tile_start, tile_id, first_plane,
+            first_plane + nplanes - 1, a, b);
     if (a == b) return;
     const int tu = tile_id / g.ntile, tv = tile_id % g.ntile;
     const int gsz = g.grid_size;
+    const size_t plane_cells = (size_t) gsz * gsz;
     const int rows_valid = min(ES_TILE, gsz - tu * ES_TILE);
     const int cols_valid = min(ES_TILE, gsz - tv * ES_TILE);
-    const T2* in = planes + (size_t) blockIdx.y * gsz * gsz +
-            (size_t) (tu * ES_TILE) * gsz + (size_t) (tv * ES_TILE);
+    const T2* in = planes + (size_t) (tu * ES_TILE) * gsz +
+            (size_t) (tv * ES_TILE);
     const int w_sup = g.support;
     const T beta = (T) g.beta;
     const T inv_hs = (T) (2.0 / (double) w_sup);
@@ -457,44 +463,58 @@ __global__ void __launch_bounds__(ES_GATHER_THREADS) es_gather_kernel(
     for (uint32_t e = a + threadIdx.x; e < b; e += ES_GATHER_THREADS)
     {
         const Rec r = records[e];
-        const int dp = plane - r.p0;
-        if (dp < 0 || dp > w_sup) continue;
-        const T kw = es_psi(beta, ((T) dp + r.dw) * inv_hs);
+        /* planes of this batch the record touches: p0 .. p0 + W */
+        const int q_lo = max(r.p0 - first_plane, 0);
+        const int q_hi = min(r.p0 + w_sup - first_plane, nplanes - 1);
+        if (q_lo > q_hi) continue;
         const int lu0 = r.lu0, lv0 = r.lv0;
-        T kv[NS];
+        T kv[NS], ku[NS];
         #pragma unroll
         for (int c = 0; c < NS; ++c)
         {
-            const int col = lv0 + c;
-            const bool ok = (c <= w_sup) && col >= 0 && col < cols_valid;
-            T k = ok ? es_psi(beta, ((T) c + r.dv) * inv_hs) : (T) 0;
-            kv[c] = (col & 1) ? -k : k;
+            const int col = lv0 + c, row = lu0 + c;
+            const bool col_ok = (c <= w_sup) && col >= 0 && col < cols_valid;
+            const bool row_ok = (c <= w_sup) && row >= 0 && row < rows_valid;
+            /* kernels.cu:201-213, with the (-1)^(gu+gv) of :233-235 folded in */
+            const T kc = col_ok ? es_psi(beta, ((T) c + r.dv) * inv_hs) : (T) 0;
+            const T kr = row_ok ? es_psi(beta, ((T) c + r.du) * inv_hs) : (T) 0;
+            kv[c] = (col & 1) ? -kc : kc;
+            ku[c] = (row & 1) ? -kr : kr;
         }
         T sum_re = (T) 0, sum_im = (T) 0;
-        for (int s = 0; s <= w_sup; ++s)
+        for (int q = q_lo; q <= q_hi; ++q)
         {
-            const int row = lu0 + s;
-            if (row < 0 || row >= rows_valid) continue;
-            T ku = es_psi(beta, ((T) s + r.du) * inv_hs);
-            if (row & 1) ku = -ku;
-            const T2* prow = in + (size_t) row * gsz + lv0;
-            T row_re = (T) 0, row_im = (T) 0;
+            const int dp = first_plane + q - r.p0;
+            const T kw = es_psi(beta, ((T) dp + r.dw) * inv_hs);
+            const T2* pl = in + (size_t) q * plane_cells + lv0;
+            T pl_re = (T) 0, pl_im = (T) 0;
             #pragma unroll
-            for (int c = 0; c < NS; ++c)
+            for (int s = 0; s < NS; ++s)
             {
-                if (kv[c] != (T) 0)
+                if (ku[s] != (T) 0)
                 {
-                    const T2 cell = prow[c];
-                    row_re += cell.x * kv[c];
-                    row_im += cell.y * kv[c];
+                    const T2* prow = pl + (size_t) (lu0 + s) * gsz;
+                    T row_re = (T) 0, row_im = (T) 0;
+                    #pragma unroll
+                    for (int c = 0; c < NS; ++c)
+                    {
+                        if (kv[c] != (T) 0)
+                        {
+                            const T2 cell = prow[c];
+                            row_re += cell.x * kv[c];
+                            row_im += cell.y * kv[c];
+                        }
+                    }
+                    pl_re += row_re * ku[s];
+                    pl_im += row_im * ku[s];
                 }
             }
-            sum_re += row_re * ku;
-            sum_im += row_im * ku;
+            sum_re += pl_re * kw;
+            sum_im += pl_im * kw;
         }
         T2 t = acc[e];
-        t.x += sum_re * kw;
-        t.y += sum_im * kw;
+        t.x += sum_re;
+        t.y += sum_im;
         acc[e] = t;
     }
 }
@@ -742,14 +762,14 @@ static int launch_gather_t(const EsGeom* g, const void* records,
 {
     typedef typename Prec<T>::T2 T2;
     typedef typename Prec<T>::Rec Rec;
-    dim3 grid((unsigned) (g->ntile * g->ntile), (unsigned) nplanes);
+    dim3 grid((unsigned) (g->ntile * g->ntile));
     if (g->support + 1 <= 9)
         es_gather_kernel<T, 9><<<grid, ES_GATHER_THREADS, 0, s>>>(*g,
-                (const Rec*) records, keys, tile_start, first_plane,
+                (const Rec*) records, keys, tile_start, first_plane, nplanes,
                 (const T2*) planes, (T2*) acc);
     else
         es_gather_kernel<T, 17><<<grid, ES_GATHER_THREADS, 0, s>>>(*g,
-                (const Rec*) records, keys, tile_start, first_plane,
+                (const Rec*) records, keys, tile_start, first_plane, nplanes,
                 (const T2*) planes, (T2*) acc);
     return (int) cudaGetLastError();
 }

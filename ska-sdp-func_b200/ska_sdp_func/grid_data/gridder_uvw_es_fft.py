@@ -87,6 +87,7 @@ class GridderUvwEsFft(StructWrapper):
         pixel_size_y_rad,
         epsilon: float,
         do_w_stacking: bool,
+        w_range=None,
     ):
         """Create a plan for (de)gridding with the given buffers' shapes.
 
@@ -95,8 +96,13 @@ class GridderUvwEsFft(StructWrapper):
         dirty_image [N, N] square; one precision and one location for all.
         epsilon is the requested accuracy; with do_w_stacking the full
         improved w-stacking algorithm is run, otherwise w is taken as zero.
+        w_range (extension, default None = derive from uvw like the reference):
+        (min |w|, max |w|) in wavelengths, for callers that need one global
+        w-plane lattice across several plans (multi-GPU).
         """
-        if do_w_stacking:
+        if do_w_stacking and w_range is not None:
+            min_abs_w, max_abs_w = w_range
+        elif do_w_stacking:
             min_abs_w, max_abs_w = GridderUvwEsFft.get_w_range(uvw, freq_hz)
         else:
             min_abs_w = 0

@@ -32,7 +32,8 @@ def reference_test_case(nxydirty=256, num_vis=1000, num_chan=10, seed=40,
         uvw = uvw.astype(np.float32)
         weight = weight.astype(np.float32)
     return dict(uvw=uvw, freq_hz=freqs, vis=vis, weight=weight, image=image,
-                pixel_size=pixel_size_rad, name=f"C1-ref-test-{nxydirty}")
+                pixel_size=pixel_size_rad, image_size=nxydirty,
+                name=f"C1-ref-test-{nxydirty}")
 
 
 def uniform_box(num_rows=1000, num_chan=1024, image_size=4096, fov_deg=2.0,
@@ -99,7 +100,7 @@ def ska_low_snapshot(num_stations=512, num_chan=1024, image_size=16384,
     image = rng.uniform(-0.5, 0.5, (image_size, image_size)) if image_size <= 4096 \
         else None
     out = dict(uvw=uvw, freq_hz=freqs, vis=vis, weight=weight, image=image,
-               pixel_size=pix,
+               pixel_size=pix, image_size=image_size,
                name=f"C4-ska-low-{num_stations}st-{num_chan}ch-{image_size}")
     return _cast(out, single)
 
@@ -160,6 +161,8 @@ def wide_field(num_rows=31250, num_chan=1024, image_size=8192, fov_deg=20.0,
 
 
 def _cast(case, single):
+    if "image_size" not in case and case.get("image") is not None:
+        case["image_size"] = case["image"].shape[0]
     real = np.float32 if single else np.float64
     cplx = np.complex64 if single else np.complex128
     for key in ("uvw", "freq_hz", "weight", "image"):
