@@ -73,6 +73,10 @@ typedef struct sdp_EsCallStats
     double ms_total, ms_presort, ms_scatter_gather, ms_fft, ms_screen;
     int32_t plane_batch;       /* w-planes resident per FFT batch */
     int32_t timing_enabled;
+    int32_t pruned_fft;        /* 1: in-shared-memory pruned line FFTs with the
+                                * w-screen fused (ms_fft = pass 1, ms_screen =
+                                * pass 2 + screen); 0: cuFFT 2-D plans */
+    int32_t reserved_;
 } sdp_EsCallStats;
 
 /* enable != 0: record CUDA-event timings per stage (adds stream syncs at the

@@ -108,6 +108,46 @@ int es_launch_correct(const EsGeom* g, void* dirty, const double* quad_kernel,
 int es_launch_plane_histogram(const EsGeom* g, const void* uvw,
         const void* freq, unsigned long long* hist, es_stream_t stream);
 
+/* ---- pruned w-plane FFT with fused w-screen (es_fft.cu) ---- */
+
+typedef struct EsFft EsFft;
+
+/* Plans the in-shared-memory line FFT for this grid / image size. Returns 0
+ * and *out on success; -1 (and *out == NULL) when the size is not supported
+ * (line does not fit in shared memory, prime factor > 11, or the environment
+ * variable SKA_SDP_FUNC_ES_USE_CUFFT is set): the caller then uses cuFFT 2-D
+ * plans; any other value is a cudaError_t. */
+int es_fft_create(int grid_size, int image_size, int is_double, EsFft** out);
+void es_fft_destroy(EsFft* fft);
+
+/* Bytes of the transposed, pruned intermediate strip[plane][N][G]. */
+size_t es_fft_strip_bytes(const EsFft* fft, int nplanes);
+
+/* Gridding pass 1: planes[q][u][:] -> inverse FFT along v -> strip[q][v'][u]. */
+int es_fft_grid_rows(const EsFft* fft, const void* planes, int nplanes,
+        void* strip, es_stream_t stream);
+
+/* Gridding pass 2: strip[q][v'][:] -> inverse FFT along u -> w-screen ->
+ * image_t[v'][u'] += sum over the nplanes planes (image_t is the transposed
+ * dirty image, N x N reals). */
+int es_fft_grid_cols_screen(const EsFft* fft, const EsGeom* g,
+        const void* strip, int first_plane, int nplanes, void* image_t,
+        es_stream_t stream);
+
+/* Degridding pass 1: image_t[v'][:] x conj w-screen, zero padded -> forward
+ * FFT along u -> strip[q][v'][u]. */
+int es_fft_degrid_cols(const EsFft* fft, const EsGeom* g, const void* image_t,
+        int first_plane, int nplanes, void* strip, es_stream_t stream);
+
+/* Degridding pass 2: strip[q][:][u] zero padded -> forward FFT along v ->
+ * planes[q][u][:]. */
+int es_fft_degrid_rows(const EsFft* fft, const void* strip, int nplanes,
+        void* planes, es_stream_t stream);
+
+/* dst[r][c] = src[c][r] (add == 0) or dst[r][c] += src[c][r], n x n reals. */
+int es_launch_transpose(const void* src, void* dst, int n, int is_double,
+        int add, es_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

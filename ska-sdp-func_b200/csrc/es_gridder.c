@@ -59,6 +59,12 @@ struct sdp_GridderUvwEsFft
     int32_t fft_batch[ES_NUM_FFT_PLANS];
     EsBuffer fft_work;
 
+    /* pruned in-shared-memory FFT with fused w-screen (es_fft.cu); NULL:
+     * cuFFT 2-D plans + separate w-screen kernels */
+    EsFft* pruned_fft;
+    EsBuffer strip;   /* plane_batch x N x G complex */
+    EsBuffer image_t; /* N x N reals: transposed image accumulator */
+
     /* presort work space (grow-only) */
     EsBuffer counts, offsets, keys_a, keys_b, vals_a, vals_b, records;
     EsBuffer tile_start, sort_temp, acc;
@@ -300,12 +306,14 @@ void sdp_gridder_uvw_es_fft_free_plan(sdp_GridderUvwEsFft* plan)
     if (!plan) return;
     for (int k = 0; k < ES_NUM_FFT_PLANS; ++k)
         if (plan->fft_batch[k] > 0) (void) cufftDestroy(plan->fft[k]);
+    es_fft_destroy(plan->pruned_fft);
     if (plan->d_quad_kernel) (void) cudaFree(plan->d_quad_kernel);
     if (plan->d_quad_nodes) (void) cudaFree(plan->d_quad_nodes);
     if (plan->d_quad_weights) (void) cudaFree(plan->d_quad_weights);
     if (plan->d_conv_corr) (void) cudaFree(plan->d_conv_corr);
     EsBuffer* all[] = {
-        &plan->planes, &plan->fft_work, &plan->counts, &plan->offsets,
+        &plan->planes, &plan->fft_work, &plan->strip, &plan->image_t,
+        &plan->counts, &plan->offsets,
         &plan->keys_a, &plan->keys_b, &plan->vals_a, &plan->vals_b,
         &plan->records, &plan->tile_start, &plan->sort_temp, &plan->acc,
         &plan->st_uvw, &plan->st_freq, &plan->st_vis, &plan->st_weight,
@@ -362,7 +370,12 @@ static int choose_plane_batch(const sdp_GridderUvwEsFft* plan)
     }
     const double plane_bytes = 2.0 * (double) real_bytes(plan) *
             (double) plan->info.grid_size * (double) plan->info.grid_size;
-    int fit = (int) (0.35 * (double) free_b / (2.0 * plane_bytes));
+    /* per resident plane: cuFFT mode = plane + an equally large work area;
+     * pruned mode = plane + its N x G strip */
+    const double per_plane = plan->pruned_fft ?
+            plane_bytes * (1.0 + (double) plan->info.image_size /
+                    (double) plan->info.grid_size) : 2.0 * plane_bytes;
+    int fit = (int) (0.35 * (double) free_b / per_plane);
     if (fit < 1) fit = 1;
     int batch = plan->info.num_total_w_grids;
     if (batch > limit) batch = limit;
@@ -464,6 +477,17 @@ sdp_GridderUvwEsFft* sdp_gridder_uvw_es_fft_create_plan(
     free(cc);
     if (!*status)
     {
+        const int rc = es_fft_create(g->grid_size, g->image_size, is_double,
+                &plan->pruned_fft);
+        if (rc > 0)
+        {
+            *status = SDP_ERR_MEM_ALLOC_FAILURE;
+            SDP_LOG_CRITICAL("GPU memory allocation failure: %s",
+                    cudaGetErrorString((cudaError_t) rc));
+        }
+    }
+    if (!*status)
+    {
         plan->plane_batch = choose_plane_batch(plan);
         const size_t plane_bytes = 2 * real_bytes(plan) *
                 (size_t) g->grid_size * (size_t) g->grid_size;
@@ -472,7 +496,17 @@ sdp_GridderUvwEsFft* sdp_gridder_uvw_es_fft_create_plan(
             sdp_Error try_status = SDP_SUCCESS;
             buffer_reserve(&plan->planes,
                     plane_bytes * (size_t) plan->plane_batch, &try_status);
+            if (plan->pruned_fft)
+            {
+                buffer_reserve(&plan->strip, es_fft_strip_bytes(
+                        plan->pruned_fft, plan->plane_batch), &try_status);
+                buffer_reserve(&plan->image_t, real_bytes(plan) *
+                        (size_t) image_size * (size_t) image_size,
+                        &try_status);
+            }
             if (!try_status) break;
+            buffer_free(&plan->planes);
+            buffer_free(&plan->strip);
             if (plan->plane_batch == 1) { *status = try_status; break; }
             plan->plane_batch /= 2;
         }
@@ -800,6 +834,7 @@ static void events_begin(sdp_GridderUvwEsFft* plan)
     memset(&plan->stats, 0, sizeof(plan->stats));
     plan->stats.plane_batch = plan->plane_batch;
     plan->stats.timing_enabled = plan->timing;
+    plan->stats.pruned_fft = plan->pruned_fft ? 1 : 0;
     plan->stage_used = 0;
     if (plan->timing && !plan->have_events)
     {
@@ -901,6 +936,9 @@ void sdp_grid_uvw_es_fft(sdp_GridderUvwEsFft* plan, const sdp_Mem* uvw,
     presort(plan, &a, 1, &m, status);
     if (*status) return;
     plan->stats.num_entries = m;
+    if (plan->pruned_fft)
+        ES_CUDA(cudaMemsetAsync(plan->image_t.ptr, 0, real_bytes(plan) *
+                (size_t) g->image_size * (size_t) g->image_size, s));
     event_mark(plan, 1);
 
     for (int first = g->plane_begin; first < g->plane_end;
@@ -914,14 +952,35 @@ void sdp_grid_uvw_es_fft(sdp_GridderUvwEsFft* plan, const sdp_Mem* uvw,
                 (const uint32_t*) plan->tile_start.ptr, first, nb,
                 plan->planes.ptr, s));
         stage_mark(plan);
-        fft_exec(plan, nb, 0, status); /* CUFFT_INVERSE, es_fft.cpp:568 */
-        if (*status) return;
-        stage_mark(plan);
-        ES_CUDA(es_launch_apply_screen(g, plan->planes.ptr, first, nb,
-                a.dirty, s));
+        if (plan->pruned_fft)
+        {
+            /* inverse transform (es_fft.cpp:568) as two pruned line passes,
+             * the second fused with the w-screen and the plane sum */
+            ES_CUDA(es_fft_grid_rows(plan->pruned_fft, plan->planes.ptr, nb,
+                    plan->strip.ptr, s));
+            stage_mark(plan);
+            ES_CUDA(es_fft_grid_cols_screen(plan->pruned_fft, g,
+                    plan->strip.ptr, first, nb, plan->image_t.ptr, s));
+            plan->stats.kernel_launches += 1;
+        }
+        else
+        {
+            fft_exec(plan, nb, 0, status); /* CUFFT_INVERSE, es_fft.cpp:568 */
+            if (*status) return;
+            stage_mark(plan);
+            ES_CUDA(es_launch_apply_screen(g, plan->planes.ptr, first, nb,
+                    a.dirty, s));
+        }
         stage_mark(plan);
         plan->stats.kernel_launches += 2;
         plan->stats.planes_processed += nb;
+    }
+    if (plan->pruned_fft)
+    {
+        /* dirty += transpose(accumulator) */
+        ES_CUDA(es_launch_transpose(plan->image_t.ptr, a.dirty,
+                g->image_size, g->is_double, 1, s));
+        plan->stats.kernel_launches += 1;
     }
     event_mark(plan, 2);
     if (plan->apply_correction)
@@ -982,17 +1041,35 @@ void sdp_ifft_degrid_uvw_es(sdp_GridderUvwEsFft* plan, const sdp_Mem* uvw,
                 s));
         plan->stats.kernel_launches += 1;
     }
+    if (plan->pruned_fft)
+    {
+        /* the line FFTs read image columns: transposed copy, once */
+        ES_CUDA(es_launch_transpose(a.dirty, plan->image_t.ptr,
+                g->image_size, g->is_double, 0, s));
+        plan->stats.kernel_launches += 1;
+    }
     for (int first = g->plane_begin; first < g->plane_end;
             first += plan->plane_batch)
     {
         int nb = g->plane_end - first;
         if (nb > plan->plane_batch) nb = plan->plane_batch;
         stage_mark(plan);
-        ES_CUDA(es_launch_reverse_screen(g, a.dirty, first, nb,
-                plan->planes.ptr, s));
-        stage_mark(plan);
-        fft_exec(plan, nb, 1, status); /* CUFFT_FORWARD, es_fft.cpp:782 */
-        if (*status) return;
+        if (plan->pruned_fft)
+        {
+            ES_CUDA(es_fft_degrid_cols(plan->pruned_fft, g,
+                    plan->image_t.ptr, first, nb, plan->strip.ptr, s));
+            stage_mark(plan);
+            ES_CUDA(es_fft_degrid_rows(plan->pruned_fft, plan->strip.ptr, nb,
+                    plan->planes.ptr, s));
+        }
+        else
+        {
+            ES_CUDA(es_launch_reverse_screen(g, a.dirty, first, nb,
+                    plan->planes.ptr, s));
+            stage_mark(plan);
+            fft_exec(plan, nb, 1, status); /* CUFFT_FORWARD, es_fft.cpp:782 */
+            if (*status) return;
+        }
         stage_mark(plan);
         ES_CUDA(es_launch_gather(g, plan->records.ptr,
                 (const uint64_t*) plan->keys_b.ptr,

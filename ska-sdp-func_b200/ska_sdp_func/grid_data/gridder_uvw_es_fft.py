@@ -66,6 +66,8 @@ class EsCallStats(ctypes.Structure):
         ("ms_screen", ctypes.c_double),
         ("plane_batch", ctypes.c_int32),
         ("timing_enabled", ctypes.c_int32),
+        ("pruned_fft", ctypes.c_int32),
+        ("reserved_", ctypes.c_int32),
     ]
 
     def as_dict(self):
