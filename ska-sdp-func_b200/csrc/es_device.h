@@ -108,6 +108,29 @@ int es_launch_correct(const EsGeom* g, void* dirty, const double* quad_kernel,
 int es_launch_plane_histogram(const EsGeom* g, const void* uvw,
         const void* freq, unsigned long long* hist, es_stream_t stream);
 
+/* ---- load-balanced work units (es_scatter.cu) ---- */
+
+size_t es_unit_bytes(void);                   /* bytes of one work unit */
+size_t es_partial_tile_bytes(int is_double);  /* bytes of one partial tile */
+
+/* Builds the work list of planes [first_plane, first_plane + nplanes):
+ * per_plane != 0: one item per (tile, plane), else one per tile for the whole
+ * range. Items with more than `split` records become several units (slices).
+ * counters: 8 x uint32 on the device ([0] = number of units afterwards);
+ * split_done: max_split x uint32 completion counters. Both are zeroed here.
+ * skip_empty != 0: items without records produce no unit. */
+int es_launch_work_plan(const EsGeom* g, const uint64_t* keys,
+        const uint32_t* tile_start, int first_plane, int nplanes,
+        int per_plane, uint32_t split, uint32_t max_units, uint32_t max_split,
+        uint32_t max_partials, int skip_empty, void* units, uint32_t* counters,
+        uint32_t* split_done, es_stream_t stream);
+
+/* Gridding: persistent CTAs execute the units; every cell of the nplanes
+ * planes is written exactly once. scratch: max_partials partial tiles. */
+int es_launch_scatter2(const EsGeom* g, const void* records, const void* units,
+        uint32_t* counters, int first_plane, void* planes, void* scratch,
+        uint32_t* split_done, es_stream_t stream);
+
 /* ---- pruned w-plane FFT with fused w-screen (es_fft.cu) ---- */
 
 typedef struct EsFft EsFft;

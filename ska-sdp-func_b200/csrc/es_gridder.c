@@ -69,6 +69,9 @@ struct sdp_GridderUvwEsFft
     EsBuffer counts, offsets, keys_a, keys_b, vals_a, vals_b, records;
     EsBuffer tile_start, sort_temp, acc;
 
+    /* load-balanced work units of the current plane batch */
+    EsBuffer units, unit_counters, split_done, partials;
+
     /* staging for host arrays */
     EsBuffer st_uvw, st_freq, st_vis, st_weight, st_dirty;
 
@@ -316,6 +319,7 @@ void sdp_gridder_uvw_es_fft_free_plan(sdp_GridderUvwEsFft* plan)
         &plan->counts, &plan->offsets,
         &plan->keys_a, &plan->keys_b, &plan->vals_a, &plan->vals_b,
         &plan->records, &plan->tile_start, &plan->sort_temp, &plan->acc,
+        &plan->units, &plan->unit_counters, &plan->split_done, &plan->partials,
         &plan->st_uvw, &plan->st_freq, &plan->st_vis, &plan->st_weight,
         &plan->st_dirty
     };
@@ -827,6 +831,44 @@ static void presort(sdp_GridderUvwEsFft* plan, const EsArrays* a,
     *num_entries = m;
 }
 
+/* ----------------------------------------------------------- work units */
+
+#define ES_MAX_SPLIT_ITEMS 65536u
+#define ES_PARTIALS_BYTES ((size_t) 512 << 20)
+#define ES_MIN_SPLIT 8192u
+
+typedef struct EsWorkLimits
+{
+    uint32_t split, max_units, max_partials;
+} EsWorkLimits;
+
+/* Sizes the unit list and the partial-tile scratch for batches of up to
+ * `nb` planes over `m` records: a (tile, plane) item with more than `split`
+ * records is cut into slices (es_scatter.cu). */
+static void work_reserve(sdp_GridderUvwEsFft* plan, int nb, int64_t m,
+        int with_partials, EsWorkLimits* lim, sdp_Error* status)
+{
+    const EsGeom* g = &plan->geom;
+    const size_t tile_bytes = es_partial_tile_bytes(g->is_double);
+    lim->max_partials = with_partials ?
+            (uint32_t) (ES_PARTIALS_BYTES / tile_bytes) : 0u;
+    uint32_t split = ES_MIN_SPLIT;
+    const char* env = getenv("SKA_SDP_FUNC_ES_SPLIT");
+    if (env && atoi(env) > 0) split = (uint32_t) atoi(env);
+    /* worst case: every record touches every plane of the batch */
+    const double visits = (double) nb * (double) m;
+    if (with_partials && visits / split > 0.5 * lim->max_partials)
+        split = (uint32_t) (visits / (0.5 * lim->max_partials)) + 1u;
+    lim->split = split;
+    const double units = (double) g->ntile * g->ntile * nb + visits / split + 64.0;
+    lim->max_units = (uint32_t) units;
+    buffer_reserve(&plan->units, (size_t) lim->max_units * es_unit_bytes(), status);
+    buffer_reserve(&plan->unit_counters, 8 * sizeof(uint32_t), status);
+    buffer_reserve(&plan->split_done, ES_MAX_SPLIT_ITEMS * sizeof(uint32_t), status);
+    if (with_partials)
+        buffer_reserve(&plan->partials, (size_t) lim->max_partials * tile_bytes, status);
+}
+
 /* --------------------------------------------------------------- timing */
 
 static void events_begin(sdp_GridderUvwEsFft* plan)
@@ -939,6 +981,9 @@ void sdp_grid_uvw_es_fft(sdp_GridderUvwEsFft* plan, const sdp_Mem* uvw,
     if (plan->pruned_fft)
         ES_CUDA(cudaMemsetAsync(plan->image_t.ptr, 0, real_bytes(plan) *
                 (size_t) g->image_size * (size_t) g->image_size, s));
+    EsWorkLimits lim;
+    work_reserve(plan, plan->plane_batch, m, 1, &lim, status);
+    if (*status) return;
     event_mark(plan, 1);
 
     for (int first = g->plane_begin; first < g->plane_end;
@@ -947,10 +992,15 @@ void sdp_grid_uvw_es_fft(sdp_GridderUvwEsFft* plan, const sdp_Mem* uvw,
         int nb = g->plane_end - first;
         if (nb > plan->plane_batch) nb = plan->plane_batch;
         stage_mark(plan);
-        ES_CUDA(es_launch_scatter(g, plan->records.ptr,
-                (const uint64_t*) plan->keys_b.ptr,
-                (const uint32_t*) plan->tile_start.ptr, first, nb,
-                plan->planes.ptr, s));
+        ES_CUDA(es_launch_work_plan(g, (const uint64_t*) plan->keys_b.ptr,
+                (const uint32_t*) plan->tile_start.ptr, first, nb, 1,
+                lim.split, lim.max_units, ES_MAX_SPLIT_ITEMS, lim.max_partials,
+                0, plan->units.ptr, (uint32_t*) plan->unit_counters.ptr,
+                (uint32_t*) plan->split_done.ptr, s));
+        ES_CUDA(es_launch_scatter2(g, plan->records.ptr, plan->units.ptr,
+                (uint32_t*) plan->unit_counters.ptr, first, plan->planes.ptr,
+                plan->partials.ptr, (uint32_t*) plan->split_done.ptr, s));
+        plan->stats.kernel_launches += 1;
         stage_mark(plan);
         if (plan->pruned_fft)
         {

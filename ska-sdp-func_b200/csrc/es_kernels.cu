@@ -30,64 +30,15 @@
 #include <cuda_runtime.h>
 #include <cub/cub.cuh>
 
+#include "es_common.cuh"
 #include "es_device.h"
 
 #define ES_C0 299792458.0           /* kernels.cu:159 */
 #define ES_PI 3.1415926535897931    /* kernels.cu:10 */
 
+using namespace es;
+
 namespace {
-
-/* ------------------------------------------------------------- records */
-
-struct __align__(16) EsRecF
-{
-    short lu0, lv0;   /* first footprint slot, in tile-local cell indices */
-    int p0;           /* first (unclipped) w-plane: ceil(pos_w - W/2) */
-    float du, dv, dw; /* (first slot - position) in u, v, w: in [-W/2, -W/2 + 1) */
-    float vre, vim;   /* scatter: weighted visibility; gather: vre = flip */
-    unsigned int idx; /* row * num_chan + chan */
-};
-
-struct __align__(16) EsRecD
-{
-    short lu0, lv0;
-    int p0;
-    double du, dv, dw;
-    double vre, vim;
-    unsigned int idx;
-    unsigned int pad0;
-    double pad1;
-};
-
-static_assert(sizeof(EsRecF) == 32, "fp32 record must be 32 bytes");
-static_assert(sizeof(EsRecD) == 64, "fp64 record must be 64 bytes");
-
-template<typename T> struct Prec;
-template<> struct Prec<float>
-{
-    typedef float2 T2;
-    typedef EsRecF Rec;
-};
-template<> struct Prec<double>
-{
-    typedef double2 T2;
-    typedef EsRecD Rec;
-};
-
-/* ------------------------------------------------------------ ES kernel */
-
-/* psi(x) = x^2 > 1 ? 0 : exp(beta (sqrt(1 - x^2) - 1)), kernels.cu:97-102 */
-__device__ __forceinline__ float es_psi(float beta, float x)
-{
-    const float t = 1.0f - x * x;
-    return (t < 0.0f) ? 0.0f : __expf(beta * (sqrtf(t) - 1.0f));
-}
-
-__device__ __forceinline__ double es_psi(double beta, double x)
-{
-    const double t = 1.0 - x * x;
-    return (t < 0.0) ? 0.0 : exp(beta * (sqrt(t) - 1.0));
-}
 
 /* Where one visibility lands. Restates kernels.cu:157-196 with fp64
  * coordinates; the footprint is described by its first slot (iu0, iv0, p0)
@@ -262,40 +213,6 @@ __global__ void __launch_bounds__(256) es_plane_histogram_kernel(EsGeom g,
     const Foot f = es_footprint<T>(g, uvw, freq, row, chan);
     if (!f.valid) return;
     atomicAdd(&hist[f.p_lo], 1ULL);
-}
-
-/* Range of sorted entries of `tile_id` that can touch a plane in
- * [plane_first, plane_last]: first owned plane in [plane_first - W,
- * plane_last]. Every thread computes it (broadcast loads). */
-__device__ __forceinline__ void es_entry_range(const EsGeom& g,
-        const uint64_t* __restrict__ keys,
-        const uint32_t* __restrict__ tile_start, int tile_id, int plane_first,
-        int plane_last, uint32_t& a, uint32_t& b)
-{
-    uint32_t lo = tile_start[tile_id];
-    const uint32_t hi = tile_start[tile_id + 1];
-    a = b = lo;
-    if (lo == hi) return;
-    const uint64_t pk = (uint64_t) (g.plane_end - g.plane_begin);
-    const uint64_t base = (uint64_t) tile_id * pk;
-    const int kp_hi = plane_last - g.plane_begin;
-    const int kp_lo = max(plane_first - g.plane_begin - g.support, 0);
-    const uint64_t key_lo = base + (uint64_t) kp_lo;
-    const uint64_t key_hi = base + (uint64_t) kp_hi; /* inclusive */
-    uint32_t l = lo, h = hi;
-    while (l < h) /* first key >= key_lo */
-    {
-        const uint32_t m = l + ((h - l) >> 1);
-        if (keys[m] < key_lo) l = m + 1; else h = m;
-    }
-    a = l;
-    h = hi;
-    while (l < h) /* first key > key_hi */
-    {
-        const uint32_t m = l + ((h - l) >> 1);
-        if (keys[m] <= key_hi) l = m + 1; else h = m;
-    }
-    b = l;
 }
 
 /* ------------------------------------------------------------- scatter */

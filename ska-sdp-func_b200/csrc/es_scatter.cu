@@ -1,0 +1,392 @@
+/*
+ * Load-balanced scatter (gridding) of the sorted visibility records onto a
+ * batch of resident w-planes, sm_100a.
+ *
+ * Replaces the reference's one-thread-per-visibility kernel with global
+ * atomics (sdp_gridder_uvw_es_fft_kernels.cu:126-270, solving = 1) and its
+ * per-plane cudaMemset (sdp_gridder_uvw_es_fft.cpp:586).
+ *
+ *   es_work_plan_kernel   one thread per (uv tile, w-plane) of the batch:
+ *                         binary search of its record range, split of ranges
+ *                         longer than `split` into slices, one work unit per
+ *                         slice appended to a list (warp-aggregated atomics).
+ *                         Real uv coverage is extremely uneven (SKA-Low: one
+ *                         64x64 tile holds ~1e7 of 1.3e8 records on the first
+ *                         planes); without the split one CTA does all of it.
+ *   es_scatter2_kernel    persistent CTAs pull units from the list. A unit
+ *                         accumulates its records into a 64x64 tile in shared
+ *                         memory WITHOUT atomics: records are staged in chunks,
+ *                         each thread evaluating the 2 (W+1) + 1 ES weights of
+ *                         one record once; then each warp owns a band of 16
+ *                         tile rows and walks the chunk, its lanes covering
+ *                         (rows x W+1 columns) of a footprint. Unsplit units
+ *                         flush the tile with coalesced 16-byte stores (this
+ *                         is also the zero fill of the plane); split units
+ *                         write partial tiles to scratch and the last slice to
+ *                         finish sums them in slice order, so the result does
+ *                         not depend on scheduling (bitwise reproducible).
+ */
+#include <stdint.h>
+
+#include <cuda_runtime.h>
+
+#include "es_common.cuh"
+#include "es_device.h"
+
+using namespace es;
+
+namespace {
+
+struct __align__(16) EsUnit
+{
+    uint32_t a, b;        /* record range of this slice */
+    int32_t tile;         /* tile index tu * ntile + tv */
+    int32_t plane_q;      /* plane within the batch */
+    int32_t num_slices;   /* K: 1 = unsplit */
+    int32_t slice;        /* 0 .. K-1 */
+    int32_t split_slot;   /* index of the completion counter (K > 1) */
+    uint32_t partial_base; /* first partial tile in scratch (K > 1) */
+};
+
+static_assert(sizeof(EsUnit) == 32, "work unit must be 32 bytes");
+
+enum { CTR_UNITS = 0, CTR_SPLIT = 1, CTR_PARTIALS = 2, CTR_NEXT = 3 };
+
+/* per_plane != 0: one item per (tile, plane); else one item per tile covering
+ * the whole plane range (gather side). */
+__global__ void __launch_bounds__(256) es_work_plan_kernel(EsGeom g,
+        const uint64_t* __restrict__ keys,
+        const uint32_t* __restrict__ tile_start, int first_plane, int nplanes,
+        int per_plane, uint32_t split, uint32_t max_units, uint32_t max_split,
+        uint32_t max_partials, int skip_empty, EsUnit* __restrict__ units,
+        uint32_t* __restrict__ counters)
+{
+    const int ntiles = g.ntile * g.ntile;
+    const int nitems = per_plane ? ntiles * nplanes : ntiles;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    uint32_t a = 0, b = 0;
+    int tile = 0, q = 0;
+    uint32_t k = 0;
+    if (i < nitems)
+    {
+        /* plane-major: the tiles of one plane are consecutive units, so the
+         * stores of concurrently running CTAs fall into the same plane rows */
+        q = per_plane ? i / ntiles : 0;
+        tile = per_plane ? i - q * ntiles : i;
+        const int p_lo = first_plane + q;
+        const int p_hi = per_plane ? p_lo : first_plane + nplanes - 1;
+        es_entry_range(g, keys, tile_start, tile, p_lo, p_hi, a, b);
+        const uint32_t n = b - a;
+        k = (n == 0 && skip_empty) ? 0u : 1u;
+        if (n > split) k = (n + split - 1) / split;
+    }
+    int split_slot = -1;
+    uint32_t partial_base = 0;
+    if (k > 1 && per_plane)
+    {
+        partial_base = atomicAdd(&counters[CTR_PARTIALS], k);
+        split_slot = (int) atomicAdd(&counters[CTR_SPLIT], 1u);
+        if (partial_base + k > max_partials || (uint32_t) split_slot >= max_split)
+        {
+            k = 1; /* out of scratch: correct, only slower */
+            split_slot = -1;
+        }
+    }
+    /* warp-aggregated allocation of k list slots */
+    uint32_t incl = k;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1)
+    {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += t;
+    }
+    const uint32_t warp_total = __shfl_sync(0xffffffffu, incl, 31);
+    uint32_t base = 0;
+    if (lane == 31 && warp_total > 0)
+        base = atomicAdd(&counters[CTR_UNITS], warp_total);
+    base = __shfl_sync(0xffffffffu, base, 31) + incl - k;
+    if (k == 0 || base + k > max_units) return; /* host sizes the list for the worst case */
+    const uint32_t n = b - a;
+    const uint32_t per = (k > 1) ? (n + k - 1) / k : n;
+    for (uint32_t s = 0; s < k; ++s)
+    {
+        EsUnit u;
+        u.a = a + s * per;
+        u.b = (s + 1 == k) ? b : a + (s + 1) * per;
+        u.tile = tile;
+        u.plane_q = q;
+        u.num_slices = (int) k;
+        u.slice = (int) s;
+        u.split_slot = split_slot;
+        u.partial_base = partial_base;
+        units[base + s] = u;
+    }
+}
+
+/* ------------------------------------------------------------- scatter */
+
+#define ES_SC_THREADS 128
+#define ES_SC_BAND (ES_TILE / (ES_SC_THREADS / 32))
+
+template<typename T> struct ScatterCfg;
+template<> struct ScatterCfg<float> { static const int CHUNK = 128; };
+template<> struct ScatterCfg<double> { static const int CHUNK = 64; };
+
+/* NS: footprint slots per axis the staging arrays hold (support + 1 <= NS). */
+template<typename T, int NS>
+__global__ void __launch_bounds__(ES_SC_THREADS) es_scatter2_kernel(EsGeom g,
+        const typename Prec<T>::Rec* __restrict__ records,
+        const EsUnit* __restrict__ units, uint32_t* __restrict__ counters,
+        int first_plane, typename Prec<T>::T2* __restrict__ planes,
+        typename Prec<T>::T2* __restrict__ scratch,
+        uint32_t* __restrict__ split_done)
+{
+    typedef typename Prec<T>::T2 T2;
+    typedef typename Prec<T>::Rec Rec;
+    constexpr int CHUNK = ScatterCfg<T>::CHUNK;
+    extern __shared__ __align__(16) unsigned char es_sc_smem[];
+    T2* tile = (T2*) es_sc_smem;                       /* [ES_TILE][ES_TILE] */
+    T* s_ku = (T*) (tile + ES_TILE * ES_TILE);         /* [CHUNK][NS] */
+    T* s_kre = s_ku + CHUNK * NS;                      /* [CHUNK][NS] */
+    T* s_kim = s_kre + CHUNK * NS;                     /* [CHUNK][NS] */
+    int* s_pos = (int*) (s_kim + CHUNK * NS);          /* [CHUNK] */
+    __shared__ uint32_t s_work;
+    __shared__ int s_last;
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int gsz = g.grid_size;
+    const int ns = g.support + 1;          /* taps per axis */
+    const int rps = 32 / ns;               /* footprint rows per warp step */
+    const int c = lane % ns, rsub = lane / ns;
+    const bool lane_active = rsub < rps;
+    const T beta = (T) g.beta;
+    const T inv_hs = (T) (2.0 / (double) g.support);
+    const uint32_t num_units = counters[CTR_UNITS];
+    constexpr int VEC = 16 / (int) sizeof(T2);
+    constexpr int VPR = ES_TILE / VEC;
+    const size_t plane_cells = (size_t) gsz * gsz;
+
+    for (;;)
+    {
+        __syncthreads(); /* s_work / tile of the previous unit no longer read */
+        if (tid == 0) s_work = atomicAdd(&counters[CTR_NEXT], 1u);
+        __syncthreads();
+        const uint32_t w = s_work;
+        if (w >= num_units) break;
+        const EsUnit u = units[w];
+        const int tu = u.tile / g.ntile, tv = u.tile - tu * g.ntile;
+        const int rows_valid = min(ES_TILE, gsz - tu * ES_TILE);
+        const int cols_valid = min(ES_TILE, gsz - tv * ES_TILE);
+        const int vec_valid = cols_valid / VEC; /* grid_size is even */
+        T2* out = planes + (size_t) u.plane_q * plane_cells +
+                (size_t) (tu * ES_TILE) * gsz + (size_t) (tv * ES_TILE);
+        if (u.a == u.b)
+        {
+            /* nothing lands here on this plane: the fused "memset" */
+            const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int v = tid; v < ES_TILE * VPR; v += ES_SC_THREADS)
+            {
+                const int r = v / VPR, cv = v % VPR;
+                if (r < rows_valid && cv < vec_valid)
+                    *reinterpret_cast<float4*>(out + (size_t) r * gsz + cv * VEC) = zero;
+            }
+            continue;
+        }
+        for (int v = tid; v < ES_TILE * VPR; v += ES_SC_THREADS)
+            reinterpret_cast<float4*>(tile)[v] = make_float4(0.f, 0.f, 0.f, 0.f);
+
+        const int plane = first_plane + u.plane_q;
+        const int band_lo = warp * ES_SC_BAND;
+        const int band_hi = min(band_lo + ES_SC_BAND, rows_valid) - 1;
+        for (uint32_t chunk = u.a; chunk < u.b; chunk += CHUNK)
+        {
+            const int n = (int) min((uint32_t) CHUNK, u.b - chunk);
+            __syncthreads(); /* staging arrays free, tile zeroed */
+            /* stage: one record per thread, every ES weight it needs once
+             * (kernels.cu:201-221, signs of :233-235 folded in) */
+            for (int e = tid; e < n; e += ES_SC_THREADS)
+            {
+                const Rec r = records[chunk + e];
+                const int dp = plane - r.p0;
+                const T kw = (dp >= 0 && dp <= g.support) ?
+                        es_psi(beta, ((T) dp + r.dw) * inv_hs) : (T) 0;
+                const T vre = r.vre * kw, vim = r.vim * kw;
+                const int lu0 = r.lu0, lv0 = r.lv0;
+                s_pos[e] = (lu0 << 16) | (lv0 & 0xffff);
+#pragma unroll
+                for (int k = 0; k < NS; ++k)
+                {
+                    if (k < ns)
+                    {
+                        T ku = es_psi(beta, ((T) k + r.du) * inv_hs);
+                        T kv = es_psi(beta, ((T) k + r.dv) * inv_hs);
+                        if ((lu0 + k) & 1) ku = -ku;
+                        if ((lv0 + k) & 1) kv = -kv;
+                        s_ku[e * NS + k] = ku;
+                        s_kre[e * NS + k] = vre * kv;
+                        s_kim[e * NS + k] = vim * kv;
+                    }
+                }
+            }
+            __syncthreads();
+            /* accumulate: this warp owns tile rows band_lo .. band_hi */
+            for (int e = 0; e < n; ++e)
+            {
+                const int pos = s_pos[e];
+                const int lu0 = pos >> 16;
+                const int r_lo = max(lu0, band_lo);
+                const int r_hi = min(lu0 + ns - 1, band_hi);
+                if (r_lo > r_hi) continue; /* warp-uniform */
+                const int col = (int) (short) (pos & 0xffff) + c;
+                if (lane_active && col >= 0 && col < cols_valid)
+                {
+                    const T pre = s_kre[e * NS + c], pim = s_kim[e * NS + c];
+                    for (int r = r_lo + rsub; r <= r_hi; r += rps)
+                    {
+                        const T ku = s_ku[e * NS + (r - lu0)];
+                        T2 cell = tile[r * ES_TILE + col];
+                        cell.x += pre * ku;
+                        cell.y += pim * ku;
+                        tile[r * ES_TILE + col] = cell;
+                    }
+                }
+            }
+        }
+        __syncthreads();
+        if (u.num_slices == 1)
+        {
+            for (int v = tid; v < ES_TILE * VPR; v += ES_SC_THREADS)
+            {
+                const int r = v / VPR, cv = v % VPR;
+                if (r < rows_valid && cv < vec_valid)
+                    *reinterpret_cast<float4*>(out + (size_t) r * gsz + cv * VEC) =
+                            reinterpret_cast<const float4*>(tile)[v];
+            }
+            continue;
+        }
+        /* split unit: publish the partial tile; the last slice to finish
+         * sums all partials in slice order and stores the result */
+        float4* part = reinterpret_cast<float4*>(scratch +
+                (size_t) (u.partial_base + (uint32_t) u.slice) * (ES_TILE * ES_TILE));
+        for (int v = tid; v < ES_TILE * VPR; v += ES_SC_THREADS)
+            part[v] = reinterpret_cast<const float4*>(tile)[v];
+        __threadfence();
+        __syncthreads();
+        if (tid == 0)
+        {
+            const uint32_t prev = atomicAdd(&split_done[u.split_slot], 1u);
+            s_last = (prev + 1u == (uint32_t) u.num_slices);
+        }
+        __syncthreads();
+        if (!s_last) continue;
+        __threadfence();
+        const T2* all = scratch + (size_t) u.partial_base * (ES_TILE * ES_TILE);
+        for (int cell = tid; cell < ES_TILE * ES_TILE; cell += ES_SC_THREADS)
+        {
+            const int r = cell / ES_TILE, cc = cell % ES_TILE;
+            if (r >= rows_valid || cc >= cols_valid) continue;
+            T sx = (T) 0, sy = (T) 0;
+            for (int s = 0; s < u.num_slices; ++s)
+            {
+                const T2 v = __ldcg(all + (size_t) s * (ES_TILE * ES_TILE) + cell);
+                sx += v.x;
+                sy += v.y;
+            }
+            T2 o; o.x = sx; o.y = sy;
+            out[(size_t) r * gsz + cc] = o;
+        }
+    }
+}
+
+template<typename T, int NS>
+size_t scatter2_smem()
+{
+    typedef typename Prec<T>::T2 T2;
+    return (size_t) ES_TILE * ES_TILE * sizeof(T2) +
+            (size_t) ScatterCfg<T>::CHUNK * (3 * NS * sizeof(T) + sizeof(int));
+}
+
+template<typename T, int NS>
+int launch_scatter2_t(const EsGeom* g, const void* records, const void* units,
+        uint32_t* counters, int first_plane, void* planes, void* scratch,
+        uint32_t* split_done, cudaStream_t s)
+{
+    typedef typename Prec<T>::T2 T2;
+    typedef typename Prec<T>::Rec Rec;
+    static int grid_size = 0;
+    const size_t smem = scatter2_smem<T, NS>();
+    if (grid_size == 0)
+    {
+        cudaError_t err = cudaFuncSetAttribute(es_scatter2_kernel<T, NS>,
+                cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
+        if (err != cudaSuccess) return (int) err;
+        int dev = 0, sms = 0, per_sm = 0;
+        err = cudaGetDevice(&dev);
+        if (err == cudaSuccess) err = cudaDeviceGetAttribute(&sms,
+                cudaDevAttrMultiProcessorCount, dev);
+        if (err == cudaSuccess) err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(
+                &per_sm, es_scatter2_kernel<T, NS>, ES_SC_THREADS, smem);
+        if (err != cudaSuccess) return (int) err;
+        if (per_sm < 1) per_sm = 1;
+        grid_size = sms * per_sm;
+    }
+    es_scatter2_kernel<T, NS><<<grid_size, ES_SC_THREADS, smem, s>>>(*g,
+            (const Rec*) records, (const EsUnit*) units, counters, first_plane,
+            (T2*) planes, (T2*) scratch, split_done);
+    return (int) cudaGetLastError();
+}
+
+} // namespace
+
+extern "C" {
+
+size_t es_unit_bytes(void)
+{
+    return sizeof(EsUnit);
+}
+
+size_t es_partial_tile_bytes(int is_double)
+{
+    return (size_t) ES_TILE * ES_TILE * (is_double ? 16 : 8);
+}
+
+int es_launch_work_plan(const EsGeom* g, const uint64_t* keys,
+        const uint32_t* tile_start, int first_plane, int nplanes,
+        int per_plane, uint32_t split, uint32_t max_units, uint32_t max_split,
+        uint32_t max_partials, int skip_empty, void* units, uint32_t* counters,
+        uint32_t* split_done, es_stream_t stream)
+{
+    cudaStream_t s = (cudaStream_t) stream;
+    cudaError_t err = cudaMemsetAsync(counters, 0, 8 * sizeof(uint32_t), s);
+    if (err == cudaSuccess && split_done && max_split > 0)
+        err = cudaMemsetAsync(split_done, 0, (size_t) max_split * sizeof(uint32_t), s);
+    if (err != cudaSuccess) return (int) err;
+    const int ntiles = g->ntile * g->ntile;
+    const int nitems = per_plane ? ntiles * nplanes : ntiles;
+    es_work_plan_kernel<<<(nitems + 255) / 256, 256, 0, s>>>(*g, keys,
+            tile_start, first_plane, nplanes, per_plane, split, max_units,
+            max_split, max_partials, skip_empty, (EsUnit*) units, counters);
+    return (int) cudaGetLastError();
+}
+
+int es_launch_scatter2(const EsGeom* g, const void* records, const void* units,
+        uint32_t* counters, int first_plane, void* planes, void* scratch,
+        uint32_t* split_done, es_stream_t stream)
+{
+    cudaStream_t s = (cudaStream_t) stream;
+    const bool wide = g->support + 1 > 9;
+    if (g->is_double)
+        return wide ?
+            launch_scatter2_t<double, 17>(g, records, units, counters,
+                    first_plane, planes, scratch, split_done, s) :
+            launch_scatter2_t<double, 9>(g, records, units, counters,
+                    first_plane, planes, scratch, split_done, s);
+    return wide ?
+        launch_scatter2_t<float, 17>(g, records, units, counters, first_plane,
+                planes, scratch, split_done, s) :
+        launch_scatter2_t<float, 9>(g, records, units, counters, first_plane,
+                planes, scratch, split_done, s);
+}
+
+} // extern "C"

@@ -177,6 +177,28 @@ def test_results_are_deterministic():
     assert np.array_equal(d0, d1)
 
 
+def test_split_heavy_tiles(monkeypatch):
+    """(tile, w-plane) items with more records than the split threshold are
+    accumulated by several CTAs and summed in slice order (es_scatter.cu):
+    same result within rounding, still bitwise reproducible."""
+    from tests.helpers import oracle_grid
+    c = synth.ska_low_snapshot(48, 16, 512, single=True, r_max=2e3)
+    d0, gridder = product_grid(c, 1e-5, True)
+    monkeypatch.setenv("SKA_SDP_FUNC_ES_SPLIT", "24")
+    d1, _ = product_grid(c, 1e-5, True, gridder)
+    d2, _ = product_grid(c, 1e-5, True, gridder)
+    monkeypatch.delenv("SKA_SDP_FUNC_ES_SPLIT")
+    assert np.array_equal(d1, d2)
+    assert not np.array_equal(d0, d1)  # the split really happened
+    assert rel_max(d1, d0) <= 1e-5     # fp32 summation order only
+    assert rel_max(d1, oracle_grid(c, 1e-5, True)) <= 1e-5
+    c64 = synth.ska_low_snapshot(32, 8, 256, single=False, r_max=2e3)
+    e0, g64 = product_grid(c64, 1e-7, True)
+    monkeypatch.setenv("SKA_SDP_FUNC_ES_SPLIT", "16")
+    e1, _ = product_grid(c64, 1e-7, True, g64)
+    assert rel_max(e1, e0) <= 1e-13
+
+
 def test_plane_partition_sums_to_full_result():
     """Multi-GPU decomposition on one device: partial dirty images over
     disjoint w-plane ranges sum to the full image; partial predictions add."""
