@@ -123,71 +123,9 @@ template<int R> ES_HD int es_bitrev(int k)
     return r;
 }
 
-template<int R> struct EsOddTab;
-template<> struct EsOddTab<3>
-{
-    ES_HD static double c(int k)
-    {
-        const double t[3] = {1.0, -0.5, -0.5};
-        return t[k];
-    }
-    ES_HD static double s(int k)
-    {
-        const double t[3] = {0.0, 0.86602540378443865, -0.86602540378443865};
-        return t[k];
-    }
-};
-template<> struct EsOddTab<5>
-{
-    ES_HD static double c(int k)
-    {
-        const double t[5] = {1.0, 0.30901699437494745, -0.80901699437494745,
-            -0.80901699437494745, 0.30901699437494745};
-        return t[k];
-    }
-    ES_HD static double s(int k)
-    {
-        const double t[5] = {0.0, 0.95105651629515353, 0.58778525229247314,
-            -0.58778525229247314, -0.95105651629515353};
-        return t[k];
-    }
-};
-template<> struct EsOddTab<7>
-{
-    ES_HD static double c(int k)
-    {
-        const double t[7] = {1.0, 0.62348980185873348, -0.22252093395631439,
-            -0.90096886790241915, -0.90096886790241915, -0.22252093395631439,
-            0.62348980185873348};
-        return t[k];
-    }
-    ES_HD static double s(int k)
-    {
-        const double t[7] = {0.0, 0.7818314824680298, 0.97492791218182362,
-            0.43388373911755812, -0.43388373911755812, -0.97492791218182362,
-            -0.7818314824680298};
-        return t[k];
-    }
-};
-template<> struct EsOddTab<11>
-{
-    ES_HD static double c(int k)
-    {
-        const double t[11] = {1.0, 0.84125353283118121, 0.41541501300188644,
-            -0.14231483827328512, -0.65486073394528510, -0.95949297361449737,
-            -0.95949297361449737, -0.65486073394528510, -0.14231483827328512,
-            0.41541501300188644, 0.84125353283118121};
-        return t[k];
-    }
-    ES_HD static double s(int k)
-    {
-        const double t[11] = {0.0, 0.54064081745559756, 0.90963199535451833,
-            0.98982144188093268, 0.75574957435425827, 0.28173255684142967,
-            -0.28173255684142967, -0.75574957435425827, -0.98982144188093268,
-            -0.90963199535451833, -0.54064081745559756};
-        return t[k];
-    }
-};
+/* cos / sin (2 pi k / R) literals (generated, tools/gen_fft_trig.py) */
+template<int R> struct EsTrigTab;
+#include "es_fft_trig.inc"
 
 /* Odd prime radix DFT in registers, natural-order output:
  * X[k], X[R-k] = (x0 + sum_m a_m cos(2 pi k m / R)) +- SGN i sum_m b_m sin(..)
@@ -216,8 +154,8 @@ ES_HD void es_dft_odd(T2 (&v)[R])
 #pragma unroll
         for (int m = 1; m <= H; ++m)
         {
-            const T cs = (T) EsOddTab<R>::c((k * m) % R);
-            const T sn = (T) EsOddTab<R>::s((k * m) % R);
+            const T cs = (T) EsTrigTab<R>::c((k * m) % R);
+            const T sn = (T) EsTrigTab<R>::s((k * m) % R);
             c.x += a[m - 1].x * cs; c.y += a[m - 1].y * cs;
             d.x += b[m - 1].x * sn; d.y += b[m - 1].y * sn;
         }
@@ -227,16 +165,111 @@ ES_HD void es_dft_odd(T2 (&v)[R])
     }
 }
 
-/* Radix-R DFT, output k left in v[es_out_slot<R>(k)]. */
+/* ---- composite radices R = A * B (Cooley-Tukey inside the registers) ----
+ * n = B n1 + n2, k = k1 + A k2:
+ *   X[k1 + A k2] = sum_n2 w_B^(n2 k2) w_R^(n2 k1) sum_n1 w_A^(n1 k1) x[B n1 + n2]
+ * i.e. B DFTs of length A over stride B, constant twiddles, A DFTs of length B
+ * over contiguous registers. All indices are compile-time after unrolling. */
+template<int R> struct EsSplit { static const int A = 0, B = 0; };
+#define ES_FFT_SPLIT(R_, A_, B_) \
+    template<> struct EsSplit<R_> { static const int A = A_, B = B_; };
+ES_FFT_SPLIT(6, 2, 3) ES_FFT_SPLIT(9, 3, 3) ES_FFT_SPLIT(10, 2, 5)
+ES_FFT_SPLIT(12, 4, 3) ES_FFT_SPLIT(14, 2, 7) ES_FFT_SPLIT(15, 3, 5)
+ES_FFT_SPLIT(18, 2, 9) ES_FFT_SPLIT(20, 4, 5) ES_FFT_SPLIT(21, 3, 7)
+ES_FFT_SPLIT(22, 2, 11) ES_FFT_SPLIT(24, 8, 3) ES_FFT_SPLIT(25, 5, 5)
+ES_FFT_SPLIT(27, 3, 9) ES_FFT_SPLIT(28, 4, 7) ES_FFT_SPLIT(30, 2, 15)
+ES_FFT_SPLIT(32, 4, 8)
+#undef ES_FFT_SPLIT
+
+template<int R> struct EsIsPow2
+{
+    static const bool value = (R == 2 || R == 4 || R == 8 || R == 16);
+};
+
+/* Radix-R DFT: output k is left in v[es_out_slot<R>(k)];
+ * es_slot_index<R>(i) is the inverse map (which output sits in v[i]). */
 template<int R> ES_HD int es_out_slot(int k)
 {
-    return (R == 2 || R == 4 || R == 8 || R == 16) ? es_bitrev<R>(k) : k;
+    if constexpr (EsSplit<R>::A != 0)
+    {
+        const int A = EsSplit<R>::A, B = EsSplit<R>::B;
+        return B * es_out_slot<A>(k % A) + es_out_slot<B>(k / A);
+    }
+    else if constexpr (EsIsPow2<R>::value) return es_bitrev<R>(k);
+    else return k;
+}
+
+template<int R> ES_HD int es_slot_index(int i)
+{
+    if constexpr (EsSplit<R>::A != 0)
+    {
+        const int A = EsSplit<R>::A, B = EsSplit<R>::B;
+        return es_slot_index<A>(i / B) + A * es_slot_index<B>(i % B);
+    }
+    else if constexpr (EsIsPow2<R>::value) return es_bitrev<R>(i);
+    else return i;
+}
+
+/* d * exp(SGN 2 pi i num / den); (num, den) fold to constants. */
+template<int DEN, int SGN, typename T, typename T2>
+ES_HD T2 es_mul_w_const(const T2 d, const int num_)
+{
+    const int num = num_ % DEN;
+    if (num == 0) return d;
+    if (4 * num == DEN) return es_mul_i<SGN>(d);
+    if (2 * num == DEN) { T2 r; r.x = -d.x; r.y = -d.y; return r; }
+    if (4 * num == 3 * DEN) return es_mul_i<-SGN>(d);
+    const T c = (T) EsTrigTab<DEN>::c(num);
+    const T s = (T) (SGN > 0 ? EsTrigTab<DEN>::s(num) : -EsTrigTab<DEN>::s(num));
+    T2 r;
+    if (8 * num == DEN || 8 * num == 5 * DEN)
+    {
+        /* c == s: (x - y) c, (x + y) c */
+        r.x = (d.x - d.y) * c;
+        r.y = (d.x + d.y) * c;
+        if (SGN < 0) { r.x = (d.x + d.y) * c; r.y = (d.y - d.x) * c; }
+        return r;
+    }
+    r.x = d.x * c - d.y * s;
+    r.y = d.x * s + d.y * c;
+    return r;
+}
+
+template<int R, int SGN, typename T, typename T2> ES_HD void es_dft(T2 (&v)[R]);
+
+template<int A, int B, int SGN, typename T, typename T2>
+ES_HD void es_dft_comp(T2 (&v)[A * B])
+{
+#pragma unroll
+    for (int n2 = 0; n2 < B; ++n2)
+    {
+        T2 t[A];
+#pragma unroll
+        for (int n1 = 0; n1 < A; ++n1) t[n1] = v[B * n1 + n2];
+        es_dft<A, SGN, T>(t);
+#pragma unroll
+        for (int i = 0; i < A; ++i)
+            v[B * i + n2] = es_mul_w_const<A * B, SGN, T>(t[i],
+                    n2 * es_slot_index<A>(i));
+    }
+#pragma unroll
+    for (int i = 0; i < A; ++i)
+    {
+        T2 t[B];
+#pragma unroll
+        for (int n2 = 0; n2 < B; ++n2) t[n2] = v[B * i + n2];
+        es_dft<B, SGN, T>(t);
+#pragma unroll
+        for (int n2 = 0; n2 < B; ++n2) v[B * i + n2] = t[n2];
+    }
 }
 
 template<int R, int SGN, typename T, typename T2>
 ES_HD void es_dft(T2 (&v)[R])
 {
-    if constexpr (R == 2 || R == 4 || R == 8 || R == 16)
+    if constexpr (EsSplit<R>::A != 0)
+        es_dft_comp<EsSplit<R>::A, EsSplit<R>::B, SGN, T>(v);
+    else if constexpr (EsIsPow2<R>::value)
         es_dft_pow2<R, SGN, T>(v);
     else
         es_dft_odd<R, SGN, T>(v);
@@ -253,82 +286,172 @@ ES_HD T2 es_twiddle(const EsFftStage& st, const T2* tw, const int j)
     return w;
 }
 
-/* Butterfly `ql` (< n / R) of one radix-R pass over the line at `x`. */
+/* One radix-R butterfly in registers: v[k] = input k on entry; output k is
+ * left in v[es_out_slot<R>(k)]. The stage twiddles w_L^(j k) are applied to
+ * the inputs (DIT) or to the outputs (DIF); their powers come from the
+ * balanced recurrence w^2m = (w^m)^2, w^(2m+1) = w^2m w. */
 template<int R, int SGN, bool DIT, typename T, typename T2>
-ES_HD void es_butterfly(T2* x, const EsFftStage& st, const T2* tw, const int ql)
+ES_HD void es_bf_core(T2 (&v)[R], const EsFftStage& st, const T2* tw,
+        const int j)
 {
-    int b, j;
-    if (st.stride == 1) { b = ql; j = 0; }
-    else
+    const bool twiddled = st.stride > 1;
+    T2 w[R];
+    if (twiddled)
     {
-        b = (int) (((float) ql + 0.5f) * st.inv_stride);
-        j = ql - b * st.stride;
-    }
-    T2* p = x + (size_t) b * st.len + j;
-    const int s = st.stride;
-    T2 v[R];
-    T2 w[R]; /* w[k] = w_L^(j k), k >= 1; built in the order of use so that
-              * only w[1] and the upper half of the computed powers stay live */
-    if (s > 1) w[1] = es_twiddle<SGN>(st, tw, j);
-    v[0] = p[0];
-#pragma unroll
-    for (int k = 1; k < R; ++k)
-    {
-        v[k] = p[k * s];
-        if (DIT && s > 1)
+        w[1] = es_twiddle<SGN>(st, tw, j);
+        if (DIT)
         {
-            if (k > 1)
-                w[k] = (k & 1) ? es_cmul(w[k - 1], w[1]) :
-                        es_cmul(w[k / 2], w[k / 2]);
-            v[k] = es_cmul(v[k], w[k]);
+#pragma unroll
+            for (int k = 1; k < R; ++k)
+            {
+                if (k > 1)
+                    w[k] = (k & 1) ? es_cmul(w[k - 1], w[1]) :
+                            es_cmul(w[k / 2], w[k / 2]);
+                v[k] = es_cmul(v[k], w[k]);
+            }
         }
     }
     es_dft<R, SGN, T>(v);
-    p[0] = v[es_out_slot<R>(0)];
-#pragma unroll
-    for (int k = 1; k < R; ++k)
+    if (twiddled && !DIT)
     {
-        T2 out = v[es_out_slot<R>(k)];
-        if (!DIT && s > 1)
+#pragma unroll
+        for (int k = 1; k < R; ++k)
         {
             if (k > 1)
                 w[k] = (k & 1) ? es_cmul(w[k - 1], w[1]) :
                         es_cmul(w[k / 2], w[k / 2]);
-            out = es_cmul(out, w[k]);
+            v[es_out_slot<R>(k)] = es_cmul(v[es_out_slot<R>(k)], w[k]);
         }
-        p[k * s] = out;
     }
 }
 
-/* One radix-R pass over `nlines` lines (pitch elements apart) by `nthreads`
- * workers, this one being `tid`. Caller synchronises between passes. */
-template<int R, int SGN, bool DIT, typename T, typename T2>
-ES_HD void es_fft_pass_r(T2* x, const EsFftStage& st, const int n,
-        const T2* tw, const int nlines, const int pitch, const int tid,
-        const int nthreads)
+/* Position of element `pos` of a line in (shared) memory: one pad of
+ * pl.pad elements after every block of pl.stage[0].stride elements, so that
+ * the digit-reversed last pass (consecutive threads stage[0].stride elements
+ * apart) is free of bank conflicts. */
+ES_HD int es_padded(const EsFftLine& pl, const int pos)
 {
-    const int per_line = n / R;
-    const int total = per_line * nlines;
-    for (int q = tid; q < total; q += nthreads)
-    {
-        int line = 0, ql = q;
-        while (ql >= per_line) { ql -= per_line; ++line; }
-        es_butterfly<R, SGN, DIT, T>(x + (size_t) line * pitch, st, tw, ql);
-    }
+    if (pl.pad == 0) return pos;
+    return pos + pl.pad * (int) (((float) pos + 0.5f) * pl.inv_stride0);
 }
 
-template<int SGN, bool DIT, typename T, typename T2>
-ES_HD void es_fft_pass(T2* x, const EsFftLine& pl, const int stage,
-        const T2* tw, const int nlines, const int pitch, const int tid,
-        const int nthreads)
+/* One pass of the line FFT over `1 << lshift` lines (pitch elements apart in
+ * x) by nthreads workers, this one being tid. step = 0 .. num_stages - 1 in
+ * processing order (DIF: stage = step, DIT: stage = num_stages - 1 - step).
+ *  - the first processed pass takes its inputs from in(line, index) instead
+ *    of x, the last one hands its outputs to out(line, index, value):
+ *      natural-stride pass (stage 0):  index = j + k * stride0
+ *      digit-reversed pass (last stage): index = t + k * (n / radix), where
+ *      consecutive butterflies t own consecutive indices and bpos[t] is the
+ *      padded position of their `radix` contiguous elements in x;
+ *  - all other traffic is in place in x (no barrier inside a pass).
+ * The caller synchronises between passes. */
+template<int R, int SGN, bool DIT, typename T, typename T2, typename In,
+        typename Out>
+ES_HD void es_line_pass_body(T2* x, const EsFftLine& pl, const int stage,
+        const bool from_in, const bool to_out, const T2* tw,
+        const int32_t* bpos, const int lshift, const int pitch, const int tid,
+        const int nthreads, In& in, Out& out)
 {
     const EsFftStage& st = pl.stage[stage];
-#define ES_FFT_CASE(R) case R: es_fft_pass_r<R, SGN, DIT, T>(x, st, pl.n, tw, \
-        nlines, pitch, tid, nthreads); break;
-    switch (st.radix)
+    const int per_line = pl.n / R;
+    const int total = per_line << lshift;
+    const int lmask = (1 << lshift) - 1;
+    const bool last_stage = (stage == pl.num_stages - 1);
+    for (int e = tid; e < total; e += nthreads)
     {
-    ES_FFT_CASE(16) ES_FFT_CASE(8) ES_FFT_CASE(4) ES_FFT_CASE(2)
-    ES_FFT_CASE(3) ES_FFT_CASE(5) ES_FFT_CASE(7) ES_FFT_CASE(11)
+        const int line = e & lmask, ql = e >> lshift;
+        T2* xl = x + (size_t) line * pitch;
+        int j = 0, base, estride, gidx, gstride;
+        if (last_stage)
+        {
+            /* stride 1: R contiguous elements, digit-reversed butterfly order */
+            base = bpos[ql];
+            estride = 1;
+            gidx = ql;
+            gstride = per_line;
+        }
+        else
+        {
+            int b;
+            if (stage == 0) { b = 0; j = ql; }
+            else
+            {
+                b = (int) (((float) ql + 0.5f) * st.inv_stride);
+                j = ql - b * st.stride;
+            }
+            const int pos = b * st.len + j;
+            base = es_padded(pl, pos);
+            /* stage 0 strides over the pads, later stages stay inside a block */
+            estride = (stage == 0) ? st.stride + pl.pad : st.stride;
+            gidx = j; /* only used by stage 0 */
+            gstride = st.stride;
+        }
+        T2 v[R];
+        if (from_in)
+        {
+#pragma unroll
+            for (int k = 0; k < R; ++k) v[k] = in(line, gidx + k * gstride);
+        }
+        else
+        {
+#pragma unroll
+            for (int k = 0; k < R; ++k) v[k] = xl[base + k * estride];
+        }
+        es_bf_core<R, SGN, DIT, T>(v, st, tw, j);
+        if (to_out)
+        {
+#pragma unroll
+            for (int k = 0; k < R; ++k)
+                out(line, gidx + k * gstride, v[es_out_slot<R>(k)]);
+        }
+        else
+        {
+#pragma unroll
+            for (int k = 0; k < R; ++k)
+                xl[base + k * estride] = v[es_out_slot<R>(k)];
+        }
+    }
+}
+
+/* fp64 butterflies above radix 16 do not fit the register file and are
+ * never planned (es_fft_line_plan): they are not instantiated. */
+#define ES_FFT_MAX_RADIX_DOUBLE 16
+
+template<int R, int SGN, bool DIT, typename T, typename T2, typename In,
+        typename Out>
+ES_HD void es_line_pass_r(T2* x, const EsFftLine& pl, const int stage,
+        const bool from_in, const bool to_out, const T2* tw,
+        const int32_t* bpos, const int lshift, const int pitch, const int tid,
+        const int nthreads, In& in, Out& out)
+{
+    if constexpr (sizeof(T) == 4 || R <= ES_FFT_MAX_RADIX_DOUBLE)
+        es_line_pass_body<R, SGN, DIT, T>(x, pl, stage, from_in, to_out, tw,
+                bpos, lshift, pitch, tid, nthreads, in, out);
+}
+
+/* Radices with a butterfly (ES_FFT_CASE is defined at the point of use). */
+#ifndef ES_FFT_RADIX_CASES
+#define ES_FFT_RADIX_CASES \
+    ES_FFT_CASE(2) ES_FFT_CASE(3) ES_FFT_CASE(4) ES_FFT_CASE(5) \
+    ES_FFT_CASE(6) ES_FFT_CASE(7) ES_FFT_CASE(8) ES_FFT_CASE(9) \
+    ES_FFT_CASE(10) ES_FFT_CASE(11) ES_FFT_CASE(12) ES_FFT_CASE(14) \
+    ES_FFT_CASE(15) ES_FFT_CASE(16) ES_FFT_CASE(20) ES_FFT_CASE(22) \
+    ES_FFT_CASE(24) ES_FFT_CASE(28) ES_FFT_CASE(32)
+#endif
+
+template<int SGN, bool DIT, typename T, typename T2, typename In, typename Out>
+ES_HD void es_line_pass(T2* x, const EsFftLine& pl, const int step,
+        const T2* tw, const int32_t* bpos, const int lshift, const int pitch,
+        const int tid, const int nthreads, In& in, Out& out)
+{
+    const int stage = DIT ? pl.num_stages - 1 - step : step;
+    const bool from_in = (step == 0), to_out = (step == pl.num_stages - 1);
+#define ES_FFT_CASE(R) case R: es_line_pass_r<R, SGN, DIT, T>(x, pl, stage, \
+        from_in, to_out, tw, bpos, lshift, pitch, tid, nthreads, in, out); break;
+    switch (pl.stage[stage].radix)
+    {
+    ES_FFT_RADIX_CASES
     default: break;
     }
 #undef ES_FFT_CASE

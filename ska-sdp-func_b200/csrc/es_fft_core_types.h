@@ -23,7 +23,9 @@ typedef struct EsFftLine
     int32_t n;
     int32_t num_stages;
     int32_t num_twiddles; /* total entries of all tables */
-    int32_t pad_;
+    int32_t pad;          /* pad elements after every stage[0].stride elements */
+    float inv_stride0;    /* 1 / stage[0].stride */
+    int32_t padded_n;     /* n + pad * stage[0].radix */
     EsFftStage stage[ES_FFT_MAX_STAGES];
 } EsFftLine;
 

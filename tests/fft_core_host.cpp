@@ -1,44 +1,71 @@
 // Host emulation of the in-shared-memory line FFT (csrc/es_fft_core.h + es_fft_plan.c):
-// the same butterflies, tables and digit-reversal map the kernels use, run one
-// "thread" at a time. Writes input then output (complex128) to a file that
-// tests/test_fft_core.py compares with numpy.fft.
+// the same passes, butterflies, tables, padding and digit-reversal maps the
+// kernels use, run one "thread" at a time over `lines` interleaved lines with
+// the first pass reading from / the last pass writing to "global" arrays
+// through functors, exactly like es_fft.cu. Writes input then output
+// (complex128, line after line) to a file that tests/test_fft_core.py compares
+// with numpy.fft.
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <vector>
 #include <cmath>
 #include "es_fft_core.h"
 #include "es_fft_plan.h"
 template<typename T> struct C2 { T x, y; };
-template<typename T, int SGN, bool DIT> int run(int n, int maxr, const char* out)
+template<typename T> struct InF
+{
+    const C2<T>* src; int n;
+    C2<T> operator()(int line, int idx) const { return src[(size_t) line * n + idx]; }
+};
+template<typename T> struct OutF
+{
+    C2<T>* dst; int n;
+    void operator()(int line, int idx, C2<T> v) const { dst[(size_t) line * n + idx] = v; }
+};
+template<typename T, int SGN, bool DIT> int run(int n, int maxr, int lshift,
+        const int32_t* forced, const char* out)
 {
     EsFftLine pl;
-    if (es_fft_line_plan(n, maxr, &pl)) { printf("unsupported %d\n", n); return 1; }
-    std::vector<double> tw(2 * pl.num_twiddles); std::vector<int32_t> perm(n);
-    es_fft_line_tables(&pl, tw.data(), perm.data());
-    std::vector<C2<T>> twt(pl.num_twiddles), x(n), in(n);
+    if (es_fft_line_plan(n, maxr, forced, &pl)) { printf("unsupported %d\n", n); return 1; }
+    const int lines = 1 << lshift;
+    std::vector<double> tw(2 * pl.num_twiddles + 2);
+    std::vector<int32_t> bpos(n / pl.stage[pl.num_stages - 1].radix);
+    es_fft_line_tables(&pl, tw.data(), 0, bpos.data());
+    const int pitch = pl.padded_n + 3;
+    std::vector<C2<T>> twt(pl.num_twiddles + 1), x((size_t) lines * pitch), in((size_t) lines * n),
+            res((size_t) lines * n);
     for (int i = 0; i < pl.num_twiddles; ++i) { twt[i].x = (T) tw[2*i]; twt[i].y = (T) tw[2*i+1]; }
     srand(n);
-    for (int i = 0; i < n; ++i) { in[i].x = (T)(rand() / (double) RAND_MAX - 0.5); in[i].y = (T)(rand() / (double) RAND_MAX - 0.5); }
-    if (DIT) for (int i = 0; i < n; ++i) x[perm[i]] = in[i]; else x = in;
-    const int nt = 512;
-    for (int s = 0; s < pl.num_stages; ++s) {
-        const int stage = DIT ? pl.num_stages - 1 - s : s;
+    for (size_t i = 0; i < in.size(); ++i) { in[i].x = (T)(rand() / (double) RAND_MAX - 0.5); in[i].y = (T)(rand() / (double) RAND_MAX - 0.5); }
+    // poison the work area: every element a pass reads must have been written
+    for (size_t i = 0; i < x.size(); ++i) { x[i].x = (T) NAN; x[i].y = (T) NAN; }
+    InF<T> fin{in.data(), n};
+    OutF<T> fout{res.data(), n};
+    const int nt = 96;
+    for (int step = 0; step < pl.num_stages; ++step)
         for (int tid = 0; tid < nt; ++tid)
-            es_fft_pass<SGN, DIT, T>(x.data(), pl, stage, twt.data(), 1, n, tid, nt);
-    }
+            es_line_pass<SGN, DIT, T>(x.data(), pl, step, twt.data(), bpos.data(), lshift,
+                    pitch, tid, nt, fin, fout);
     FILE* f = fopen(out, "wb");
-    for (int i = 0; i < n; ++i) { double v[2] = {(double) in[i].x, (double) in[i].y}; fwrite(v, 8, 2, f); }
-    for (int i = 0; i < n; ++i) { C2<T> r = DIT ? x[i] : x[perm[i]]; double v[2] = {(double) r.x, (double) r.y}; fwrite(v, 8, 2, f); }
+    for (size_t i = 0; i < in.size(); ++i) { double v[2] = {(double) in[i].x, (double) in[i].y}; fwrite(v, 8, 2, f); }
+    for (size_t i = 0; i < res.size(); ++i) { double v[2] = {(double) res[i].x, (double) res[i].y}; fwrite(v, 8, 2, f); }
     fclose(f);
-    printf("n=%d stages:", n); for (int s = 0; s < pl.num_stages; ++s) printf(" %d", pl.stage[s].radix); printf(" tw=%d\n", pl.num_twiddles);
+    printf("n=%d stages:", n); for (int s = 0; s < pl.num_stages; ++s) printf(" %d", pl.stage[s].radix);
+    printf(" tw=%d pad=%d\n", pl.num_twiddles, pl.pad);
     return 0;
 }
+// fft_core_host n double sign dit lshift out [r0,r1,...]
 int main(int argc, char** argv)
 {
     int n = atoi(argv[1]); int dbl = atoi(argv[2]); int sgn = atoi(argv[3]); int dit = atoi(argv[4]);
-    const char* out = argv[5];
-    if (dbl) { if (sgn > 0) return dit ? run<double, 1, true>(n, 8, out) : run<double, 1, false>(n, 8, out);
-               else return dit ? run<double, -1, true>(n, 8, out) : run<double, -1, false>(n, 8, out); }
-    if (sgn > 0) return dit ? run<float, 1, true>(n, 16, out) : run<float, 1, false>(n, 16, out);
-    return dit ? run<float, -1, true>(n, 16, out) : run<float, -1, false>(n, 16, out);
+    int lshift = atoi(argv[5]);
+    const char* out = argv[6];
+    int32_t forced[ES_FFT_MAX_STAGES + 1]; memset(forced, 0, sizeof(forced));
+    if (argc > 7) { int c = 0; for (char* p = strtok(argv[7], ","); p && c < ES_FFT_MAX_STAGES; p = strtok(0, ",")) forced[c++] = atoi(p); }
+    const int32_t* fr = forced[0] ? forced : 0;
+    if (dbl) { if (sgn > 0) return dit ? run<double, 1, true>(n, 16, lshift, fr, out) : run<double, 1, false>(n, 16, lshift, fr, out);
+               else return dit ? run<double, -1, true>(n, 16, lshift, fr, out) : run<double, -1, false>(n, 16, lshift, fr, out); }
+    if (sgn > 0) return dit ? run<float, 1, true>(n, 32, lshift, fr, out) : run<float, 1, false>(n, 32, lshift, fr, out);
+    return dit ? run<float, -1, true>(n, 32, lshift, fr, out) : run<float, -1, false>(n, 32, lshift, fr, out);
 }

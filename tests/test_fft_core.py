@@ -27,26 +27,58 @@ def exe():
 
 
 # grid sizes of BASELINE configs C1..C5, the reference test (1540, 1920) and odd cases
-SIZES = [392, 1540, 1920, 6160, 11520, 14400, 24640, 98, 120, 2 * 3 * 5 * 7 * 11]
+SIZES = [392, 1540, 1920, 6160, 11520, 14400, 24640, 98, 120, 28, 44, 2 * 3 * 5 * 7 * 11]
+
+
+def _check(exe, n, double, lshift, out, radices=None):
+    lines = 1 << lshift
+    for sign in (1, -1):
+        for dit in (0, 1):
+            cmd = [exe, str(n), str(double), str(sign), str(dit), str(lshift), out]
+            if radices:
+                cmd.append(radices)
+            r = subprocess.run(cmd, check=True, capture_output=True, text=True)
+            assert "unsupported" not in r.stdout, r.stdout
+            d = np.fromfile(out, dtype=np.complex128).reshape(2, lines, n)
+            x, y = d[0], d[1]
+            ref = np.fft.ifft(x, axis=1) * n if sign > 0 else np.fft.fft(x, axis=1)
+            err = np.max(np.abs(y - ref)) / np.max(np.abs(ref))
+            assert err < (1e-14 if double else 2e-6), (n, double, sign, dit, err)
 
 
 @pytest.mark.parametrize("n", SIZES)
 @pytest.mark.parametrize("double", [0, 1])
 def test_line_fft_matches_numpy(exe, n, double, tmp_path):
+    _check(exe, n, double, 0, str(tmp_path / "fft.bin"))
+
+
+@pytest.mark.parametrize("lshift", [1, 2])
+def test_interleaved_lines(exe, lshift, tmp_path):
+    """bundles of 2 / 4 lines share one pass (column kernels)"""
+    _check(exe, 1540, 0, lshift, str(tmp_path / "fft.bin"))
+    _check(exe, 392, 1, lshift, str(tmp_path / "fft.bin"))
+
+
+# every butterfly radix at least once, as first, middle and last pass
+@pytest.mark.parametrize("radices", [
+    "32,28,3", "3,28,32", "24,22,5", "5,24,22", "20,15,14", "14,20,15", "12,10,9",
+    "9,12,10", "16,6,11", "11,16,6", "8,7,4", "4,2,7", "2,3,5,7,11", "6,6", "30"])
+def test_forced_radices(exe, radices, tmp_path):
+    vals = [int(v) for v in radices.split(",")]
+    n = int(np.prod(vals))
     out = str(tmp_path / "fft.bin")
-    for sign in (1, -1):
-        for dit in (0, 1):
-            subprocess.run([exe, str(n), str(double), str(sign), str(dit), out],
-                           check=True, capture_output=True)
-            d = np.fromfile(out, dtype=np.complex128)
-            x, y = d[:n], d[n:]
-            ref = np.fft.ifft(x) * n if sign > 0 else np.fft.fft(x)
-            err = np.max(np.abs(y - ref)) / np.max(np.abs(ref))
-            assert err < (1e-14 if double else 2e-6), (n, double, sign, dit, err)
+    if 30 in vals:  # no butterfly for 30
+        r = subprocess.run([exe, str(n), "0", "1", "0", "0", out, radices],
+                           capture_output=True, text=True)
+        assert "unsupported" in r.stdout
+        return
+    _check(exe, n, 0, 0, out, radices)
+    if max(vals) <= 16:
+        _check(exe, n, 1, 1, out, radices)
 
 
 def test_unsupported_sizes_are_reported(exe, tmp_path):
     out = str(tmp_path / "fft.bin")
-    r = subprocess.run([exe, str(2 * 13), "0", "1", "0", out], capture_output=True,
+    r = subprocess.run([exe, str(2 * 13), "0", "1", "0", "0", out], capture_output=True,
                        text=True)
     assert "unsupported" in r.stdout
