@@ -41,6 +41,7 @@
 #include "es_device.h"
 #include "es_fft_core.h"
 #include "es_fft_plan.h"
+#include "es_screen.h"
 
 #define ES_FFT_THREADS 512 /* upper bound of the CTA size (128 registers each) */
 #define ES_FFT_MAX_SMEM (227 * 1024)
@@ -60,6 +61,8 @@ struct EsFft
     int32_t grid_size, image_size, is_double;
     EsFftCfg rows;    /* one line per CTA */
     EsFftCfg cols;    /* 1 << lshift adjacent columns per CTA */
+    int32_t bs;       /* log2 run length of the blocked intermediate */
+    int64_t plane_elems; /* elements of the intermediate per plane */
 };
 
 namespace {
@@ -83,50 +86,31 @@ template<typename T> struct Screen;
 
 template<> struct Screen<float>
 {
-    __device__ __forceinline__ static void eval(const double sos, const double w,
-            const double sign, float& re, float& im, float& inv_n)
+    /* s2 = iu^2 + jv^2; w_signed = sign * w (es_screen.h) */
+    __device__ __forceinline__ static void eval(const uint32_t s2,
+            const double pix2, const float pix2f, const double w_signed,
+            float& re, float& im, float& inv_n)
     {
-        const double a = 1.0 - sos;
-        double y = (double) rsqrtf((float) a);
-        y = y * (1.5 - 0.5 * a * y * y);     /* 1 / n */
-        const double nm1 = a * y - 1.0;      /* n - 1 */
-        double t = w * nm1;
-        t -= rint(t);
-        sincospif((float) (2.0 * sign * t), &im, &re);
-        inv_n = (float) y;
+        es_screen_f32(s2, pix2, pix2f, w_signed, re, im, inv_n);
     }
 };
 
 template<> struct Screen<double>
 {
-    __device__ __forceinline__ static void eval(const double sos, const double w,
-            const double sign, double& re, double& im, double& inv_n)
+    __device__ __forceinline__ static void eval(const uint32_t s2,
+            const double pix2, const float, const double w_signed,
+            double& re, double& im, double& inv_n)
     {
+        const double sos = pix2 * (double) s2;
         const double nm1 = (-sos) / (sqrt(1.0 - sos) + 1.0);
-        double t = w * nm1;
+        double t = w_signed * nm1;
         t -= rint(t);
-        sincospi(2.0 * sign * t, &im, &re);
+        sincospi(2.0 * t, &im, &re);
         inv_n = 1.0 / (nm1 + 1.0);
     }
 };
 
 /* ------------------------------------------------ global-memory functors */
-
-/* plane row / T row: contiguous line, optional window [k0, k0 + count) */
-template<typename T2> struct RowIn
-{
-    const T2* src;
-    int k0, count; /* element idx lives at src[idx - k0] when inside */
-    unsigned int any;
-    __device__ __forceinline__ T2 operator()(int, int idx)
-    {
-        T2 v;
-        v.x = 0; v.y = 0;
-        const int r = idx - k0;
-        if ((unsigned) r < (unsigned) count) v = src[r];
-        return v;
-    }
-};
 
 /* whole plane row, remembers whether anything was non-zero */
 struct RowInAnyF
@@ -157,6 +141,7 @@ template<typename T> struct RowInAny;
 template<> struct RowInAny<float> { typedef RowInAnyF type; };
 template<> struct RowInAny<double> { typedef RowInAnyD type; };
 
+/* contiguous line with a window: element idx at dst[idx - k0] */
 template<typename T2> struct RowOut
 {
     T2* dst;
@@ -168,25 +153,46 @@ template<typename T2> struct RowOut
     }
 };
 
-/* bundle of adjacent columns of T: element idx of line l at src[idx * n + l] */
-template<typename T2> struct ColIn
+/* The pruned intermediate T (strip) is laid out so that the pass that WRITES
+ * it scatters single elements (the neighbouring lines, transformed by CTAs
+ * that run at the same time, complete the sectors in L2) and the pass that
+ * READS it finds runs of B = 2^bs consecutive elements of its line:
+ *   gridding    T[u >> bs][v'][u & (B - 1)]   written by rows u, read by columns v'
+ *   degridding  T[v' >> bs][u][v' & (B - 1)]  written by columns v', read by rows u
+ * bs = 0 with bundles of adjacent columns is the row-major variant T[u][v'].
+ *
+ * Writer side: element (idx - k0) of the line at base + (idx - k0) * stride
+ * (+ line * lstride for bundles). */
+template<typename T2> struct StridedOut
 {
-    const T2* src;
-    size_t n;
-    unsigned int any;
-    __device__ __forceinline__ T2 operator()(int line, int idx)
+    T2* base;
+    size_t stride, lstride;
+    int k0, count;
+    __device__ __forceinline__ void operator()(int line, int idx, const T2 v) const
     {
-        return src[(size_t) idx * n + line];
+        const int r = idx - k0;
+        if ((unsigned) r < (unsigned) count)
+            base[(size_t) r * stride + (size_t) line * lstride] = v;
     }
 };
 
-template<typename T2> struct ColOut
+/* Reader side: element r = idx - k0 of the line at
+ * base + (r >> bs) * outer + (r & (B - 1)) (+ line * lstride); zero outside
+ * the window [k0, k0 + count). */
+template<typename T2> struct BlockedIn
 {
-    T2* dst;
-    size_t n;
-    __device__ __forceinline__ void operator()(int line, int idx, const T2 v) const
+    const T2* base;
+    size_t outer, lstride;
+    int bs, k0, count;
+    __device__ __forceinline__ T2 operator()(int line, int idx) const
     {
-        dst[(size_t) idx * n + line] = v;
+        T2 v;
+        v.x = 0; v.y = 0;
+        const int r = idx - k0;
+        if ((unsigned) r < (unsigned) count)
+            v = base[(size_t) (r >> bs) * outer + (size_t) (r & ((1 << bs) - 1)) +
+                    (size_t) line * lstride];
+        return v;
     }
 };
 
@@ -198,6 +204,7 @@ template<typename T, typename T2> struct ScreenOut
     int jv0;        /* first column - n / 2 */
     int wstack;
     double pix2, w;
+    float pix2f;
     __device__ __forceinline__ void operator()(int line, int idx, const T2 v) const
     {
         const int iu = idx - gh;
@@ -207,9 +214,9 @@ template<typename T, typename T2> struct ScreenOut
         if (wstack)
         {
             /* iu^2 + jv^2 < 2^31 for images up to 32768^2 */
-            const double sos = pix2 * (double) (iu * iu + jv * jv);
             T cr, ci, inv_n;
-            Screen<T>::eval(sos, w, -1.0, cr, ci, inv_n);
+            Screen<T>::eval((uint32_t) (iu * iu + jv * jv), pix2, pix2f, -w,
+                    cr, ci, inv_n);
             val = (v.x * cr - v.y * ci) * inv_n;
         }
         if ((iu + jv) & 1) val = -val;
@@ -224,7 +231,7 @@ template<typename T, typename T2> struct ScreenIn
     const T* image_t;
     int n, half, gh, jv0, wstack;
     double pix2, w;
-    unsigned int any;
+    float pix2f;
     __device__ __forceinline__ T2 operator()(int line, int idx)
     {
         T2 o;
@@ -236,9 +243,9 @@ template<typename T, typename T2> struct ScreenIn
         if ((iu + jv) & 1) d = -d;
         if (wstack)
         {
-            const double sos = pix2 * (double) (iu * iu + jv * jv);
             T cr, ci, inv_n;
-            Screen<T>::eval(sos, w, 1.0, cr, ci, inv_n);
+            Screen<T>::eval((uint32_t) (iu * iu + jv * jv), pix2, pix2f, w,
+                    cr, ci, inv_n);
             d *= inv_n;
             o.x = cr * d;
             o.y = ci * d;
@@ -267,6 +274,15 @@ __device__ __forceinline__ void fft_all_passes(T2* x, const EsFftLine& pl,
     }
 }
 
+/* Layout of the intermediate and CTA shape, by value to the kernels. */
+struct EsFftLayout
+{
+    int32_t bs;        /* log2 of the run length B of the blocked layouts */
+    int32_t lshift;    /* log2 of the columns per CTA of the column kernels */
+    int32_t rows_pitch, cols_pitch;
+    int64_t plane_elems; /* elements of T per plane */
+};
+
 /* ------------------------------------------------------ gridding pass 1 */
 
 template<typename T>
@@ -275,26 +291,29 @@ __global__ void __launch_bounds__(ES_FFT_THREADS, 1) es_fft_grid_rows_kernel(
         const int32_t* __restrict__ bpos,
         const typename Cx<T>::T2* __restrict__ planes,
         typename Cx<T>::T2* __restrict__ strip, const int image_size,
-        const int pitch)
+        const EsFftLayout lay)
 {
     typedef typename Cx<T>::T2 T2;
     extern __shared__ __align__(16) unsigned char es_fft_smem[];
     T2* x = (T2*) es_fft_smem;
-    T2* tw = x + pitch;
+    T2* tw = x + lay.rows_pitch;
     const int gsz = pl.n, n = image_size;
-    const size_t row = (size_t) blockIdx.y * gsz + blockIdx.x;
+    const int u = blockIdx.x;
     typename RowInAny<T>::type in;
-    in.src = planes + row * gsz;
+    in.src = planes + ((size_t) blockIdx.y * gsz + u) * gsz;
     in.any = 0u;
-    RowOut<T2> out;
-    out.dst = strip + row * n;
+    StridedOut<T2> out;
+    out.base = strip + (size_t) blockIdx.y * lay.plane_elems +
+            (((size_t) (u >> lay.bs) * n) << lay.bs) + (u & ((1 << lay.bs) - 1));
+    out.stride = (size_t) 1 << lay.bs;
+    out.lstride = 0;
     out.k0 = gsz / 2 - n / 2;
     out.count = n;
     load_twiddles(tw, tw_g, pl.num_twiddles);
     __syncthreads();
     for (int step = 0; step < pl.num_stages; ++step)
     {
-        es_line_pass<1, false, T>(x, pl, step, tw, bpos, 0, pitch,
+        es_line_pass<1, false, T>(x, pl, step, tw, bpos, 0, lay.rows_pitch,
                 (int) threadIdx.x, (int) blockDim.x, in, out);
         if (step + 1 == pl.num_stages) break;
         if (step == 0)
@@ -304,7 +323,8 @@ __global__ void __launch_bounds__(ES_FFT_THREADS, 1) es_fft_grid_rows_kernel(
             {
                 T2 zero;
                 zero.x = 0; zero.y = 0;
-                for (int i = threadIdx.x; i < n; i += blockDim.x) out.dst[i] = zero;
+                for (int i = threadIdx.x; i < n; i += blockDim.x)
+                    out.base[(size_t) i * out.stride] = zero;
                 return;
             }
         }
@@ -317,9 +337,9 @@ __global__ void __launch_bounds__(ES_FFT_THREADS, 1) es_fft_grid_rows_kernel(
 
 /* ------------------------------------------------------ gridding pass 2 */
 
-/* One CTA per bundle of adjacent columns v': the planes of the batch are
- * transformed one after the other and summed into the imageT slice of the
- * bundle (which stays in L2 meanwhile). A pixel always receives its
+/* One CTA per column v' (or bundle of adjacent columns): the planes of the
+ * batch are transformed one after the other and summed into the imageT slice
+ * of the column (which stays in L2 meanwhile). A pixel always receives its
  * contributions from the same thread in plane order, so the sum does not
  * depend on scheduling (bitwise reproducible). */
 template<typename T>
@@ -328,17 +348,20 @@ es_fft_grid_cols_screen_kernel(const EsFftLine pl,
         const typename Cx<T>::T2* __restrict__ tw_g,
         const int32_t* __restrict__ bpos, const EsGeom g,
         const typename Cx<T>::T2* __restrict__ strip, const int first_plane,
-        const int nplanes, T* __restrict__ image_t, const int lshift,
-        const int pitch)
+        const int nplanes, T* __restrict__ image_t, const EsFftLayout lay)
 {
     typedef typename Cx<T>::T2 T2;
     extern __shared__ __align__(16) unsigned char es_fft_smem[];
     T2* x = (T2*) es_fft_smem;
-    T2* tw = x + ((size_t) pitch << lshift);
+    T2* tw = x + ((size_t) lay.cols_pitch << lay.lshift);
     const int gsz = pl.n, n = g.image_size;
-    const int col0 = blockIdx.x << lshift;
-    ColIn<T2> in;
-    in.n = (size_t) n;
+    const int col0 = blockIdx.x << lay.lshift;
+    BlockedIn<T2> in;
+    in.outer = (size_t) n << lay.bs;
+    in.lstride = (size_t) 1 << lay.bs;
+    in.bs = lay.bs;
+    in.k0 = 0;
+    in.count = gsz;
     ScreenOut<T, T2> out;
     out.image_t = image_t + (size_t) col0 * n + n / 2;
     out.n = n;
@@ -347,13 +370,15 @@ es_fft_grid_cols_screen_kernel(const EsFftLine pl,
     out.jv0 = col0 - n / 2;
     out.wstack = g.do_wstacking;
     out.pix2 = g.pixel_size * g.pixel_size;
+    out.pix2f = (float) out.pix2;
     load_twiddles(tw, tw_g, pl.num_twiddles);
     for (int q = 0; q < nplanes; ++q)
     {
         __syncthreads(); /* twiddles loaded / previous plane's last pass done */
-        in.src = strip + (size_t) q * gsz * n + col0;
+        in.base = strip + (size_t) q * lay.plane_elems + ((size_t) col0 << lay.bs);
         out.w = (double) (first_plane + q) * g.inv_w_scale + g.min_plane_w;
-        fft_all_passes<1, false, T>(x, pl, tw, bpos, lshift, pitch, in, out);
+        fft_all_passes<1, false, T>(x, pl, tw, bpos, lay.lshift, lay.cols_pitch,
+                in, out);
     }
 }
 
@@ -365,15 +390,15 @@ __global__ void __launch_bounds__(ES_FFT_THREADS, 1) es_fft_degrid_cols_kernel(
         const int32_t* __restrict__ bpos, const EsGeom g,
         const T* __restrict__ image_t, const int first_plane,
         const int nplanes, typename Cx<T>::T2* __restrict__ strip,
-        const int lshift, const int pitch)
+        const EsFftLayout lay)
 {
     typedef typename Cx<T>::T2 T2;
     extern __shared__ __align__(16) unsigned char es_fft_smem[];
     T2* x = (T2*) es_fft_smem;
-    T2* tw = x + ((size_t) pitch << lshift);
+    T2* tw = x + ((size_t) lay.cols_pitch << lay.lshift);
     const int gsz = pl.n, n = g.image_size;
     const int q = blockIdx.x % nplanes;
-    const int col0 = (blockIdx.x / nplanes) << lshift;
+    const int col0 = (blockIdx.x / nplanes) << lay.lshift;
     ScreenIn<T, T2> in;
     in.image_t = image_t + (size_t) col0 * n + n / 2;
     in.n = n;
@@ -382,13 +407,31 @@ __global__ void __launch_bounds__(ES_FFT_THREADS, 1) es_fft_degrid_cols_kernel(
     in.jv0 = col0 - n / 2;
     in.wstack = g.do_wstacking;
     in.pix2 = g.pixel_size * g.pixel_size;
+    in.pix2f = (float) in.pix2;
     in.w = (double) (first_plane + q) * g.inv_w_scale + g.min_plane_w;
-    ColOut<T2> out;
-    out.dst = strip + (size_t) q * gsz * n + col0;
-    out.n = (size_t) n;
+    StridedOut<T2> out;
+    T2* tq = strip + (size_t) q * lay.plane_elems;
+    if (lay.lshift == 0)
+    {
+        /* T[v' >> bs][u][v' & (B - 1)] */
+        out.base = tq + (((size_t) (col0 >> lay.bs) * gsz) << lay.bs) +
+                (col0 & ((1 << lay.bs) - 1));
+        out.stride = (size_t) 1 << lay.bs;
+        out.lstride = 0;
+    }
+    else
+    {
+        /* row-major T[u][v'], bundle of adjacent columns */
+        out.base = tq + col0;
+        out.stride = (size_t) n;
+        out.lstride = 1;
+    }
+    out.k0 = 0;
+    out.count = gsz;
     load_twiddles(tw, tw_g, pl.num_twiddles);
     __syncthreads();
-    fft_all_passes<-1, true, T>(x, pl, tw, bpos, lshift, pitch, in, out);
+    fft_all_passes<-1, true, T>(x, pl, tw, bpos, lay.lshift, lay.cols_pitch,
+            in, out);
 }
 
 /* ---------------------------------------------------- degridding pass 2 */
@@ -399,25 +442,38 @@ __global__ void __launch_bounds__(ES_FFT_THREADS, 1) es_fft_degrid_rows_kernel(
         const int32_t* __restrict__ bpos,
         const typename Cx<T>::T2* __restrict__ strip,
         typename Cx<T>::T2* __restrict__ planes, const int image_size,
-        const int pitch)
+        const EsFftLayout lay)
 {
     typedef typename Cx<T>::T2 T2;
     extern __shared__ __align__(16) unsigned char es_fft_smem[];
     T2* x = (T2*) es_fft_smem;
-    T2* tw = x + pitch;
+    T2* tw = x + lay.rows_pitch;
     const int gsz = pl.n, n = image_size;
-    const size_t row = (size_t) blockIdx.y * gsz + blockIdx.x;
-    RowIn<T2> in;
-    in.src = strip + row * n;
+    const int u = blockIdx.x;
+    BlockedIn<T2> in;
+    const T2* tq = strip + (size_t) blockIdx.y * lay.plane_elems;
+    if (lay.lshift == 0)
+    {
+        in.base = tq + ((size_t) u << lay.bs);
+        in.outer = (size_t) gsz << lay.bs;
+        in.bs = lay.bs;
+    }
+    else
+    {
+        in.base = tq + (size_t) u * n;
+        in.outer = 1;
+        in.bs = 0;
+    }
+    in.lstride = 0;
     in.k0 = gsz / 2 - n / 2;
     in.count = n;
     RowOut<T2> out;
-    out.dst = planes + row * gsz;
+    out.dst = planes + ((size_t) blockIdx.y * gsz + u) * gsz;
     out.k0 = 0;
     out.count = gsz;
     load_twiddles(tw, tw_g, pl.num_twiddles);
     __syncthreads();
-    fft_all_passes<-1, true, T>(x, pl, tw, bpos, 0, pitch, in, out);
+    fft_all_passes<-1, true, T>(x, pl, tw, bpos, 0, lay.rows_pitch, in, out);
 }
 
 /* ------------------------------------------------------ image transposes */
@@ -491,6 +547,17 @@ void make_cfg(const EsFftLine* line, size_t cplx, int lshift, int threads,
     c->threads = threads;
 }
 
+EsFftLayout fft_layout(const EsFft* f)
+{
+    EsFftLayout lay;
+    lay.bs = f->bs;
+    lay.lshift = f->cols.lshift;
+    lay.rows_pitch = f->rows.pitch;
+    lay.cols_pitch = f->cols.pitch;
+    lay.plane_elems = f->plane_elems;
+    return lay;
+}
+
 template<typename K>
 int fft_set_smem(K kernel, size_t bytes)
 {
@@ -539,21 +606,34 @@ int es_fft_create(int grid_size, int image_size, int is_double, EsFft** out)
     f->image_size = image_size;
     f->is_double = is_double;
     const size_t cplx = is_double ? 16 : 8;
-    /* experiments: SKA_SDP_FUNC_ES_FFT_CFG="rows_threads,cols_threads,cols_lshift" */
-    int e[3] = {0, 0, -1};
+    /* experiments: SKA_SDP_FUNC_ES_FFT_CFG="rows_threads,cols_threads,cols_lshift,bs"
+     * default: row-major intermediate (bs = 0), bundles of 4 (fp64: 2)
+     * adjacent columns per CTA where they fit in shared memory;
+     * cols_lshift = 0 with bs > 0: blocked intermediate with runs of 2^bs
+     * elements, one column per CTA (measured slower: the scattered 8-byte
+     * stores of the row pass cost more than the bundles save,
+     * profiles/README.md) */
+    int e[4] = {0, 0, is_double ? 1 : 2, 0};
     const char* env = getenv("SKA_SDP_FUNC_ES_FFT_CFG");
-    if (env) (void) sscanf(env, "%d,%d,%d", &e[0], &e[1], &e[2]);
+    if (env) (void) sscanf(env, "%d,%d,%d,%d", &e[0], &e[1], &e[2], &e[3]);
     for (int k = 0; k < 2; ++k)
         if (e[k] < 0 || e[k] > ES_FFT_THREADS || (e[k] & 31)) e[k] = 0;
+    if (e[2] < 0 || e[2] > 2) e[2] = 0;
+    if (e[3] < 0 || e[3] > 6) e[3] = 0;
     make_cfg(&f->line, cplx, 0, e[0], &f->rows);
-    /* widest bundle of columns (32 bytes) that fits and divides the image */
-    int lshift = is_double ? 1 : 2;
-    if (e[2] >= 0 && e[2] <= 2) lshift = e[2];
+    int lshift = e[2];
     for (;; --lshift)
     {
         make_cfg(&f->line, cplx, lshift, e[1], &f->cols);
         if ((f->cols.smem_bytes <= ES_FFT_MAX_SMEM &&
                 image_size % (1 << lshift) == 0) || lshift == 0) break;
+    }
+    f->bs = lshift > 0 ? 0 : e[3];
+    {
+        const int64_t blk = (int64_t) 1 << f->bs;
+        const int64_t a = ((grid_size + blk - 1) / blk) * blk * image_size;
+        const int64_t b = ((image_size + blk - 1) / blk) * blk * grid_size;
+        f->plane_elems = a > b ? a : b;
     }
     if (f->rows.smem_bytes > ES_FFT_MAX_SMEM ||
             f->cols.smem_bytes > ES_FFT_MAX_SMEM)
@@ -567,8 +647,9 @@ int es_fft_create(int grid_size, int image_size, int is_double, EsFft** out)
         for (int k = 0; k < f->line.num_stages; ++k)
             fprintf(stderr, " %d", f->line.stage[k].radix);
         fprintf(stderr, "; pad %d; rows %d thr (%zu B), cols %d thr x %d lines "
-                "(%zu B)\n", f->line.pad, f->rows.threads, f->rows.smem_bytes,
-                f->cols.threads, 1 << f->cols.lshift, f->cols.smem_bytes);
+                "(%zu B), runs of %d\n", f->line.pad, f->rows.threads,
+                f->rows.smem_bytes, f->cols.threads, 1 << f->cols.lshift,
+                f->cols.smem_bytes, 1 << f->bs);
     }
 
     const int nt = f->line.num_twiddles;
@@ -632,26 +713,26 @@ void es_fft_destroy(EsFft* f)
 
 size_t es_fft_strip_bytes(const EsFft* f, int nplanes)
 {
-    return (size_t) nplanes * (size_t) f->image_size * (size_t) f->grid_size *
-            (f->is_double ? 16 : 8);
+    return (size_t) nplanes * (size_t) f->plane_elems * (f->is_double ? 16 : 8);
 }
 
 int es_fft_grid_rows(const EsFft* f, const void* planes, int nplanes,
         void* strip, es_stream_t stream)
 {
     cudaStream_t s = (cudaStream_t) stream;
+    const EsFftLayout lay = fft_layout(f);
     const EsFftCfg& c = f->rows;
     dim3 grid((unsigned) f->grid_size, (unsigned) nplanes);
     if (f->is_double)
         es_fft_grid_rows_kernel<double><<<grid, c.threads, c.smem_bytes,
                 s>>>(f->line, (const double2*) f->d_tw, f->d_bpos,
                 (const double2*) planes, (double2*) strip, f->image_size,
-                c.pitch);
+                lay);
     else
         es_fft_grid_rows_kernel<float><<<grid, c.threads, c.smem_bytes,
                 s>>>(f->line, (const float2*) f->d_tw, f->d_bpos,
                 (const float2*) planes, (float2*) strip, f->image_size,
-                c.pitch);
+                lay);
     return (int) cudaGetLastError();
 }
 
@@ -659,18 +740,19 @@ int es_fft_grid_cols_screen(const EsFft* f, const EsGeom* g, const void* strip,
         int first_plane, int nplanes, void* image_t, es_stream_t stream)
 {
     cudaStream_t s = (cudaStream_t) stream;
+    const EsFftLayout lay = fft_layout(f);
     const EsFftCfg& c = f->cols;
     dim3 grid((unsigned) (f->image_size >> c.lshift));
     if (f->is_double)
         es_fft_grid_cols_screen_kernel<double><<<grid, c.threads,
                 c.smem_bytes, s>>>(f->line, (const double2*) f->d_tw,
                 f->d_bpos, *g, (const double2*) strip, first_plane, nplanes,
-                (double*) image_t, c.lshift, c.pitch);
+                (double*) image_t, lay);
     else
         es_fft_grid_cols_screen_kernel<float><<<grid, c.threads,
                 c.smem_bytes, s>>>(f->line, (const float2*) f->d_tw,
                 f->d_bpos, *g, (const float2*) strip, first_plane, nplanes,
-                (float*) image_t, c.lshift, c.pitch);
+                (float*) image_t, lay);
     return (int) cudaGetLastError();
 }
 
@@ -678,18 +760,19 @@ int es_fft_degrid_cols(const EsFft* f, const EsGeom* g, const void* image_t,
         int first_plane, int nplanes, void* strip, es_stream_t stream)
 {
     cudaStream_t s = (cudaStream_t) stream;
+    const EsFftLayout lay = fft_layout(f);
     const EsFftCfg& c = f->cols;
     dim3 grid((unsigned) ((f->image_size >> c.lshift) * nplanes));
     if (f->is_double)
         es_fft_degrid_cols_kernel<double><<<grid, c.threads, c.smem_bytes,
                 s>>>(f->line, (const double2*) f->d_tw, f->d_bpos, *g,
                 (const double*) image_t, first_plane, nplanes,
-                (double2*) strip, c.lshift, c.pitch);
+                (double2*) strip, lay);
     else
         es_fft_degrid_cols_kernel<float><<<grid, c.threads, c.smem_bytes,
                 s>>>(f->line, (const float2*) f->d_tw, f->d_bpos, *g,
                 (const float*) image_t, first_plane, nplanes,
-                (float2*) strip, c.lshift, c.pitch);
+                (float2*) strip, lay);
     return (int) cudaGetLastError();
 }
 
@@ -697,18 +780,19 @@ int es_fft_degrid_rows(const EsFft* f, const void* strip, int nplanes,
         void* planes, es_stream_t stream)
 {
     cudaStream_t s = (cudaStream_t) stream;
+    const EsFftLayout lay = fft_layout(f);
     const EsFftCfg& c = f->rows;
     dim3 grid((unsigned) f->grid_size, (unsigned) nplanes);
     if (f->is_double)
         es_fft_degrid_rows_kernel<double><<<grid, c.threads, c.smem_bytes,
                 s>>>(f->line, (const double2*) f->d_tw, f->d_bpos,
                 (const double2*) strip, (double2*) planes, f->image_size,
-                c.pitch);
+                lay);
     else
         es_fft_degrid_rows_kernel<float><<<grid, c.threads, c.smem_bytes,
                 s>>>(f->line, (const float2*) f->d_tw, f->d_bpos,
                 (const float2*) strip, (float2*) planes, f->image_size,
-                c.pitch);
+                lay);
     return (int) cudaGetLastError();
 }
 

@@ -82,3 +82,17 @@ def test_unsupported_sizes_are_reported(exe, tmp_path):
     r = subprocess.run([exe, str(2 * 13), "0", "1", "0", "0", out], capture_output=True,
                        text=True)
     assert "unsupported" in r.stdout
+
+
+def test_screen_phasor_matches_libm(tmp_path):
+    """csrc/es_screen.h: the fp32 w-screen phasor without conversion / special
+    function instructions, against libm (max abs error of cos/sin, max rel
+    error of 1/n, max abs error of the sincos polynomial)."""
+    exe_path = os.path.join(ROOT, "build", "screen_host")
+    os.makedirs(os.path.dirname(exe_path), exist_ok=True)
+    subprocess.run(["g++", "-std=c++17", "-O2", "-I", CSRC,
+                    os.path.join(ROOT, "tests", "screen_host.cpp"), "-lm", "-o", exe_path],
+                   check=True)
+    r = subprocess.run([exe_path], check=True, capture_output=True, text=True)
+    ph, inv, sc = (float(v) for v in r.stdout.split())
+    assert ph < 4e-7 and inv < 2e-7 and sc < 2e-7, r.stdout
