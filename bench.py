@@ -169,6 +169,17 @@ class ClockSampler:
 
 # --------------------------------------------------------------- CPU arms
 
+def host_cores(omp_default):
+    """Threads for the CPU arms: every core this process may run on. torchrun
+    exports OMP_NUM_THREADS=1 to its workers, which would otherwise make the
+    reference arm single-threaded."""
+    try:
+        avail = len(os.sched_getaffinity(0))
+    except AttributeError:
+        avail = os.cpu_count() or 1
+    return max(int(omp_default), avail)
+
+
 def cpu_reference_gridder(case, eps, wstack, info):
     """(callable(planes) -> seconds, kind, cores, description)."""
     from oracle import es_oracle as eo, ref_oracle as ro
@@ -180,7 +191,7 @@ def cpu_reference_gridder(case, eps, wstack, info):
             mn, mx = ro.get_w_range(case["uvw"], case["freq_hz"])
             g = ro.RefHostGridder(rows, chans, n, case["pixel_size"], eps, wstack,
                                   mn, mx, 4 if single else 8, 4 if single else 8)
-            cores = ro.lib().oref_max_threads()
+            cores = host_cores(ro.lib().oref_max_threads())
 
             def run(planes):
                 t0 = time.perf_counter()
@@ -196,7 +207,7 @@ def cpu_reference_gridder(case, eps, wstack, info):
     o = eo.OracleGridder(case["uvw"], case["freq_hz"], case["vis"], case["weight"],
                          np.zeros((n, n), dtype=case["uvw"].dtype),
                          case["pixel_size"], case["pixel_size"], eps, wstack)
-    cores = eo.lib().eso_max_threads()
+    cores = host_cores(eo.lib().eso_max_threads())
 
     def run_port(planes):
         t0 = time.perf_counter()

@@ -61,7 +61,6 @@ struct EsFft
     int32_t grid_size, image_size, is_double;
     EsFftCfg rows;    /* one line per CTA */
     EsFftCfg cols;    /* 1 << lshift adjacent columns per CTA */
-    int32_t bs;       /* log2 run length of the blocked intermediate */
     int64_t plane_elems; /* elements of the intermediate per plane */
 };
 
@@ -110,117 +109,112 @@ template<> struct Screen<double>
     }
 };
 
-/* ------------------------------------------------ global-memory functors */
+/* ------------------------------------------------ global-memory functors
+ * (cursor protocol of es_line_pass: element k of a butterfly is index
+ * idx0 + k * gs of line `line`). All of them address linearly,
+ *   base + (idx - k0) * estride + line * lstride,
+ * so a cursor is one pointer and one stride; WINDOW: indices outside
+ * [k0, k0 + count) read as zero / are not stored (the pruning). */
 
-/* whole plane row, remembers whether anything was non-zero */
-struct RowInAnyF
+template<typename T2, bool WINDOW, bool ANY> struct LinearIn
 {
-    const float2* src;
-    unsigned int any;
-    __device__ __forceinline__ float2 operator()(int, int idx)
+    struct Cursor
     {
-        const float2 v = src[idx];
-        any |= (__float_as_uint(v.x) | __float_as_uint(v.y)) << 1; /* -0 is empty too */
-        return v;
-    }
-};
-
-struct RowInAnyD
-{
-    const double2* src;
-    unsigned int any;
-    __device__ __forceinline__ double2 operator()(int, int idx)
-    {
-        const double2 v = src[idx];
-        any |= (v.x != 0.0 || v.y != 0.0) ? 1u : 0u;
-        return v;
-    }
-};
-
-template<typename T> struct RowInAny;
-template<> struct RowInAny<float> { typedef RowInAnyF type; };
-template<> struct RowInAny<double> { typedef RowInAnyD type; };
-
-/* contiguous line with a window: element idx at dst[idx - k0] */
-template<typename T2> struct RowOut
-{
-    T2* dst;
+        const T2* p;
+        ptrdiff_t step;
+        int r0, gs;
+    };
+    const T2* base;          /* element k0 of line 0 */
+    ptrdiff_t estride, lstride;
     int k0, count;
-    __device__ __forceinline__ void operator()(int, int idx, const T2 v) const
+    unsigned int any;        /* ANY: becomes non-zero when a loaded value is */
+    __device__ __forceinline__ Cursor cursor(int line, int idx0, int gs) const
     {
-        const int r = idx - k0;
-        if ((unsigned) r < (unsigned) count) dst[r] = v;
+        Cursor c;
+        c.r0 = idx0 - k0;
+        c.gs = gs;
+        c.p = base + (ptrdiff_t) c.r0 * estride + (ptrdiff_t) line * lstride;
+        c.step = (ptrdiff_t) gs * estride;
+        return c;
     }
-};
-
-/* The pruned intermediate T (strip) is laid out so that the pass that WRITES
- * it scatters single elements (the neighbouring lines, transformed by CTAs
- * that run at the same time, complete the sectors in L2) and the pass that
- * READS it finds runs of B = 2^bs consecutive elements of its line:
- *   gridding    T[u >> bs][v'][u & (B - 1)]   written by rows u, read by columns v'
- *   degridding  T[v' >> bs][u][v' & (B - 1)]  written by columns v', read by rows u
- * bs = 0 with bundles of adjacent columns is the row-major variant T[u][v'].
- *
- * Writer side: element (idx - k0) of the line at base + (idx - k0) * stride
- * (+ line * lstride for bundles). */
-template<typename T2> struct StridedOut
-{
-    T2* base;
-    size_t stride, lstride;
-    int k0, count;
-    __device__ __forceinline__ void operator()(int line, int idx, const T2 v) const
-    {
-        const int r = idx - k0;
-        if ((unsigned) r < (unsigned) count)
-            base[(size_t) r * stride + (size_t) line * lstride] = v;
-    }
-};
-
-/* Reader side: element r = idx - k0 of the line at
- * base + (r >> bs) * outer + (r & (B - 1)) (+ line * lstride); zero outside
- * the window [k0, k0 + count). */
-template<typename T2> struct BlockedIn
-{
-    const T2* base;
-    size_t outer, lstride;
-    int bs, k0, count;
-    __device__ __forceinline__ T2 operator()(int line, int idx) const
+    __device__ __forceinline__ T2 load(const Cursor& c, int k)
     {
         T2 v;
         v.x = 0; v.y = 0;
-        const int r = idx - k0;
-        if ((unsigned) r < (unsigned) count)
-            v = base[(size_t) (r >> bs) * outer + (size_t) (r & ((1 << bs) - 1)) +
-                    (size_t) line * lstride];
+        if (!WINDOW || (unsigned) (c.r0 + k * c.gs) < (unsigned) count)
+            v = c.p[k * c.step];
+        if (ANY) any |= (v.x != 0 || v.y != 0) ? 1u : 0u;
         return v;
+    }
+};
+
+template<typename T2, bool WINDOW> struct LinearOut
+{
+    struct Cursor
+    {
+        T2* p;
+        ptrdiff_t step;
+        int r0, gs;
+    };
+    T2* base;
+    ptrdiff_t estride, lstride;
+    int k0, count;
+    __device__ __forceinline__ Cursor cursor(int line, int idx0, int gs) const
+    {
+        Cursor c;
+        c.r0 = idx0 - k0;
+        c.gs = gs;
+        c.p = base + (ptrdiff_t) c.r0 * estride + (ptrdiff_t) line * lstride;
+        c.step = (ptrdiff_t) gs * estride;
+        return c;
+    }
+    __device__ __forceinline__ void store(const Cursor& c, int k, const T2 v) const
+    {
+        if (!WINDOW || (unsigned) (c.r0 + k * c.gs) < (unsigned) count)
+            c.p[k * c.step] = v;
     }
 };
 
 /* gridding pass 2 output: w-screen and sum into imageT (kernels.cu:444-515) */
 template<typename T, typename T2> struct ScreenOut
 {
-    T* image_t;     /* imageT + first column of the bundle * n + n / 2 */
+    struct Cursor
+    {
+        T* p;        /* imageT element of (line, iu0) */
+        int iu0, gs, jv;
+        uint32_t jv2;
+    };
+    T* image_t;      /* imageT + first column of the bundle * n + n / 2 */
     int n, half, gh; /* image size, n / 2, grid_size / 2 */
-    int jv0;        /* first column - n / 2 */
+    int jv0;         /* first column - n / 2 */
     int wstack;
     double pix2, w;
     float pix2f;
-    __device__ __forceinline__ void operator()(int line, int idx, const T2 v) const
+    __device__ __forceinline__ Cursor cursor(int line, int idx0, int gs) const
     {
-        const int iu = idx - gh;
-        if (iu < -half || iu >= half) return;
-        const int jv = jv0 + line;
+        Cursor c;
+        c.iu0 = idx0 - gh;
+        c.gs = gs;
+        c.jv = jv0 + line;
+        c.jv2 = (uint32_t) (c.jv * c.jv);
+        c.p = image_t + (ptrdiff_t) line * n + c.iu0;
+        return c;
+    }
+    __device__ __forceinline__ void store(const Cursor& c, int k, const T2 v) const
+    {
+        const int iu = c.iu0 + k * c.gs;
+        if ((unsigned) (iu + half) >= (unsigned) n) return;
         T val = v.x;
         if (wstack)
         {
             /* iu^2 + jv^2 < 2^31 for images up to 32768^2 */
             T cr, ci, inv_n;
-            Screen<T>::eval((uint32_t) (iu * iu + jv * jv), pix2, pix2f, -w,
+            Screen<T>::eval((uint32_t) (iu * iu) + c.jv2, pix2, pix2f, -w,
                     cr, ci, inv_n);
             val = (v.x * cr - v.y * ci) * inv_n;
         }
-        if ((iu + jv) & 1) val = -val;
-        atomicAdd(image_t + (size_t) line * n + iu, val);
+        if ((iu + c.jv) & 1) val = -val;
+        atomicAdd(c.p + k * c.gs, val);
     }
 };
 
@@ -228,23 +222,38 @@ template<typename T, typename T2> struct ScreenOut
  * (kernels.cu:580-676) */
 template<typename T, typename T2> struct ScreenIn
 {
+    struct Cursor
+    {
+        const T* p;
+        int iu0, gs, jv;
+        uint32_t jv2;
+    };
     const T* image_t;
     int n, half, gh, jv0, wstack;
     double pix2, w;
     float pix2f;
-    __device__ __forceinline__ T2 operator()(int line, int idx)
+    __device__ __forceinline__ Cursor cursor(int line, int idx0, int gs) const
+    {
+        Cursor c;
+        c.iu0 = idx0 - gh;
+        c.gs = gs;
+        c.jv = jv0 + line;
+        c.jv2 = (uint32_t) (c.jv * c.jv);
+        c.p = image_t + (ptrdiff_t) line * n + c.iu0;
+        return c;
+    }
+    __device__ __forceinline__ T2 load(const Cursor& c, int k) const
     {
         T2 o;
         o.x = 0; o.y = 0;
-        const int iu = idx - gh;
-        if (iu < -half || iu >= half) return o;
-        const int jv = jv0 + line;
-        T d = image_t[(size_t) line * n + iu];
-        if ((iu + jv) & 1) d = -d;
+        const int iu = c.iu0 + k * c.gs;
+        if ((unsigned) (iu + half) >= (unsigned) n) return o;
+        T d = c.p[k * c.gs];
+        if ((iu + c.jv) & 1) d = -d;
         if (wstack)
         {
             T cr, ci, inv_n;
-            Screen<T>::eval((uint32_t) (iu * iu + jv * jv), pix2, pix2f, w,
+            Screen<T>::eval((uint32_t) (iu * iu) + c.jv2, pix2, pix2f, w,
                     cr, ci, inv_n);
             d *= inv_n;
             o.x = cr * d;
@@ -274,13 +283,12 @@ __device__ __forceinline__ void fft_all_passes(T2* x, const EsFftLine& pl,
     }
 }
 
-/* Layout of the intermediate and CTA shape, by value to the kernels. */
+/* CTA shapes and size of the intermediate, by value to the kernels. */
 struct EsFftLayout
 {
-    int32_t bs;        /* log2 of the run length B of the blocked layouts */
     int32_t lshift;    /* log2 of the columns per CTA of the column kernels */
     int32_t rows_pitch, cols_pitch;
-    int64_t plane_elems; /* elements of T per plane */
+    int64_t plane_elems; /* elements of T per plane (grid_size x image_size) */
 };
 
 /* ------------------------------------------------------ gridding pass 1 */
@@ -299,13 +307,16 @@ __global__ void __launch_bounds__(ES_FFT_THREADS, 1) es_fft_grid_rows_kernel(
     T2* tw = x + lay.rows_pitch;
     const int gsz = pl.n, n = image_size;
     const int u = blockIdx.x;
-    typename RowInAny<T>::type in;
-    in.src = planes + ((size_t) blockIdx.y * gsz + u) * gsz;
+    LinearIn<T2, false, true> in;
+    in.base = planes + ((size_t) blockIdx.y * gsz + u) * gsz;
+    in.estride = 1;
+    in.lstride = 0;
+    in.k0 = 0;
+    in.count = gsz;
     in.any = 0u;
-    StridedOut<T2> out;
-    out.base = strip + (size_t) blockIdx.y * lay.plane_elems +
-            (((size_t) (u >> lay.bs) * n) << lay.bs) + (u & ((1 << lay.bs) - 1));
-    out.stride = (size_t) 1 << lay.bs;
+    LinearOut<T2, true> out;
+    out.base = strip + (size_t) blockIdx.y * lay.plane_elems + (size_t) u * n;
+    out.estride = 1;
     out.lstride = 0;
     out.k0 = gsz / 2 - n / 2;
     out.count = n;
@@ -324,7 +335,7 @@ __global__ void __launch_bounds__(ES_FFT_THREADS, 1) es_fft_grid_rows_kernel(
                 T2 zero;
                 zero.x = 0; zero.y = 0;
                 for (int i = threadIdx.x; i < n; i += blockDim.x)
-                    out.base[(size_t) i * out.stride] = zero;
+                    out.base[i] = zero;
                 return;
             }
         }
@@ -337,9 +348,9 @@ __global__ void __launch_bounds__(ES_FFT_THREADS, 1) es_fft_grid_rows_kernel(
 
 /* ------------------------------------------------------ gridding pass 2 */
 
-/* One CTA per column v' (or bundle of adjacent columns): the planes of the
- * batch are transformed one after the other and summed into the imageT slice
- * of the column (which stays in L2 meanwhile). A pixel always receives its
+/* One CTA per bundle of adjacent columns v': the planes of the batch are
+ * transformed one after the other and summed into the imageT slice of the
+ * bundle (which stays in L2 meanwhile). A pixel always receives its
  * contributions from the same thread in plane order, so the sum does not
  * depend on scheduling (bitwise reproducible). */
 template<typename T>
@@ -356,12 +367,12 @@ es_fft_grid_cols_screen_kernel(const EsFftLine pl,
     T2* tw = x + ((size_t) lay.cols_pitch << lay.lshift);
     const int gsz = pl.n, n = g.image_size;
     const int col0 = blockIdx.x << lay.lshift;
-    BlockedIn<T2> in;
-    in.outer = (size_t) n << lay.bs;
-    in.lstride = (size_t) 1 << lay.bs;
-    in.bs = lay.bs;
+    LinearIn<T2, false, false> in;
+    in.estride = n;
+    in.lstride = 1;
     in.k0 = 0;
     in.count = gsz;
+    in.any = 0u;
     ScreenOut<T, T2> out;
     out.image_t = image_t + (size_t) col0 * n + n / 2;
     out.n = n;
@@ -375,7 +386,7 @@ es_fft_grid_cols_screen_kernel(const EsFftLine pl,
     for (int q = 0; q < nplanes; ++q)
     {
         __syncthreads(); /* twiddles loaded / previous plane's last pass done */
-        in.base = strip + (size_t) q * lay.plane_elems + ((size_t) col0 << lay.bs);
+        in.base = strip + (size_t) q * lay.plane_elems + col0;
         out.w = (double) (first_plane + q) * g.inv_w_scale + g.min_plane_w;
         fft_all_passes<1, false, T>(x, pl, tw, bpos, lay.lshift, lay.cols_pitch,
                 in, out);
@@ -409,23 +420,10 @@ __global__ void __launch_bounds__(ES_FFT_THREADS, 1) es_fft_degrid_cols_kernel(
     in.pix2 = g.pixel_size * g.pixel_size;
     in.pix2f = (float) in.pix2;
     in.w = (double) (first_plane + q) * g.inv_w_scale + g.min_plane_w;
-    StridedOut<T2> out;
-    T2* tq = strip + (size_t) q * lay.plane_elems;
-    if (lay.lshift == 0)
-    {
-        /* T[v' >> bs][u][v' & (B - 1)] */
-        out.base = tq + (((size_t) (col0 >> lay.bs) * gsz) << lay.bs) +
-                (col0 & ((1 << lay.bs) - 1));
-        out.stride = (size_t) 1 << lay.bs;
-        out.lstride = 0;
-    }
-    else
-    {
-        /* row-major T[u][v'], bundle of adjacent columns */
-        out.base = tq + col0;
-        out.stride = (size_t) n;
-        out.lstride = 1;
-    }
+    LinearOut<T2, false> out;
+    out.base = strip + (size_t) q * lay.plane_elems + col0;
+    out.estride = n;
+    out.lstride = 1;
     out.k0 = 0;
     out.count = gsz;
     load_twiddles(tw, tw_g, pl.num_twiddles);
@@ -450,25 +448,17 @@ __global__ void __launch_bounds__(ES_FFT_THREADS, 1) es_fft_degrid_rows_kernel(
     T2* tw = x + lay.rows_pitch;
     const int gsz = pl.n, n = image_size;
     const int u = blockIdx.x;
-    BlockedIn<T2> in;
-    const T2* tq = strip + (size_t) blockIdx.y * lay.plane_elems;
-    if (lay.lshift == 0)
-    {
-        in.base = tq + ((size_t) u << lay.bs);
-        in.outer = (size_t) gsz << lay.bs;
-        in.bs = lay.bs;
-    }
-    else
-    {
-        in.base = tq + (size_t) u * n;
-        in.outer = 1;
-        in.bs = 0;
-    }
+    LinearIn<T2, true, false> in;
+    in.base = strip + (size_t) blockIdx.y * lay.plane_elems + (size_t) u * n;
+    in.estride = 1;
     in.lstride = 0;
     in.k0 = gsz / 2 - n / 2;
     in.count = n;
-    RowOut<T2> out;
-    out.dst = planes + ((size_t) blockIdx.y * gsz + u) * gsz;
+    in.any = 0u;
+    LinearOut<T2, false> out;
+    out.base = planes + ((size_t) blockIdx.y * gsz + u) * gsz;
+    out.estride = 1;
+    out.lstride = 0;
     out.k0 = 0;
     out.count = gsz;
     load_twiddles(tw, tw_g, pl.num_twiddles);
@@ -550,7 +540,6 @@ void make_cfg(const EsFftLine* line, size_t cplx, int lshift, int threads,
 EsFftLayout fft_layout(const EsFft* f)
 {
     EsFftLayout lay;
-    lay.bs = f->bs;
     lay.lshift = f->cols.lshift;
     lay.rows_pitch = f->rows.pitch;
     lay.cols_pitch = f->cols.pitch;
@@ -606,20 +595,15 @@ int es_fft_create(int grid_size, int image_size, int is_double, EsFft** out)
     f->image_size = image_size;
     f->is_double = is_double;
     const size_t cplx = is_double ? 16 : 8;
-    /* experiments: SKA_SDP_FUNC_ES_FFT_CFG="rows_threads,cols_threads,cols_lshift,bs"
-     * default: row-major intermediate (bs = 0), bundles of 4 (fp64: 2)
-     * adjacent columns per CTA where they fit in shared memory;
-     * cols_lshift = 0 with bs > 0: blocked intermediate with runs of 2^bs
-     * elements, one column per CTA (measured slower: the scattered 8-byte
-     * stores of the row pass cost more than the bundles save,
-     * profiles/README.md) */
-    int e[4] = {0, 0, is_double ? 1 : 2, 0};
+    /* experiments: SKA_SDP_FUNC_ES_FFT_CFG="rows_threads,cols_threads,cols_lshift"
+     * default: bundles of 4 (fp64: 2) adjacent columns per CTA where they fit
+     * in shared memory (32-byte pieces of the row-major intermediate) */
+    int e[3] = {0, 0, is_double ? 1 : 2};
     const char* env = getenv("SKA_SDP_FUNC_ES_FFT_CFG");
-    if (env) (void) sscanf(env, "%d,%d,%d,%d", &e[0], &e[1], &e[2], &e[3]);
+    if (env) (void) sscanf(env, "%d,%d,%d", &e[0], &e[1], &e[2]);
     for (int k = 0; k < 2; ++k)
         if (e[k] < 0 || e[k] > ES_FFT_THREADS || (e[k] & 31)) e[k] = 0;
     if (e[2] < 0 || e[2] > 2) e[2] = 0;
-    if (e[3] < 0 || e[3] > 6) e[3] = 0;
     make_cfg(&f->line, cplx, 0, e[0], &f->rows);
     int lshift = e[2];
     for (;; --lshift)
@@ -628,13 +612,7 @@ int es_fft_create(int grid_size, int image_size, int is_double, EsFft** out)
         if ((f->cols.smem_bytes <= ES_FFT_MAX_SMEM &&
                 image_size % (1 << lshift) == 0) || lshift == 0) break;
     }
-    f->bs = lshift > 0 ? 0 : e[3];
-    {
-        const int64_t blk = (int64_t) 1 << f->bs;
-        const int64_t a = ((grid_size + blk - 1) / blk) * blk * image_size;
-        const int64_t b = ((image_size + blk - 1) / blk) * blk * grid_size;
-        f->plane_elems = a > b ? a : b;
-    }
+    f->plane_elems = (int64_t) grid_size * image_size;
     if (f->rows.smem_bytes > ES_FFT_MAX_SMEM ||
             f->cols.smem_bytes > ES_FFT_MAX_SMEM)
     {
@@ -647,9 +625,9 @@ int es_fft_create(int grid_size, int image_size, int is_double, EsFft** out)
         for (int k = 0; k < f->line.num_stages; ++k)
             fprintf(stderr, " %d", f->line.stage[k].radix);
         fprintf(stderr, "; pad %d; rows %d thr (%zu B), cols %d thr x %d lines "
-                "(%zu B), runs of %d\n", f->line.pad, f->rows.threads,
+                "(%zu B)\n", f->line.pad, f->rows.threads,
                 f->rows.smem_bytes, f->cols.threads, 1 << f->cols.lshift,
-                f->cols.smem_bytes, 1 << f->bs);
+                f->cols.smem_bytes);
     }
 
     const int nt = f->line.num_twiddles;

@@ -338,8 +338,10 @@ ES_HD int es_padded(const EsFftLine& pl, const int pos)
 /* One pass of the line FFT over `1 << lshift` lines (pitch elements apart in
  * x) by nthreads workers, this one being tid. step = 0 .. num_stages - 1 in
  * processing order (DIF: stage = step, DIT: stage = num_stages - 1 - step).
- *  - the first processed pass takes its inputs from in(line, index) instead
- *    of x, the last one hands its outputs to out(line, index, value):
+ *  - the first processed pass takes its inputs from `in` instead of x, the
+ *    last one hands its outputs to `out`; both are addressed through a cursor
+ *    c = cursor(line, index0, index_stride), element k of the butterfly being
+ *    index0 + k * index_stride (load(c, k) / store(c, k, value)):
  *      natural-stride pass (stage 0):  index = j + k * stride0
  *      digit-reversed pass (last stage): index = t + k * (n / radix), where
  *      consecutive butterflies t own consecutive indices and bpos[t] is the
@@ -390,8 +392,9 @@ ES_HD void es_line_pass_body(T2* x, const EsFftLine& pl, const int stage,
         T2 v[R];
         if (from_in)
         {
+            const typename In::Cursor c = in.cursor(line, gidx, gstride);
 #pragma unroll
-            for (int k = 0; k < R; ++k) v[k] = in(line, gidx + k * gstride);
+            for (int k = 0; k < R; ++k) v[k] = in.load(c, k);
         }
         else
         {
@@ -401,9 +404,10 @@ ES_HD void es_line_pass_body(T2* x, const EsFftLine& pl, const int stage,
         es_bf_core<R, SGN, DIT, T>(v, st, tw, j);
         if (to_out)
         {
+            const typename Out::Cursor c = out.cursor(line, gidx, gstride);
 #pragma unroll
             for (int k = 0; k < R; ++k)
-                out(line, gidx + k * gstride, v[es_out_slot<R>(k)]);
+                out.store(c, k, v[es_out_slot<R>(k)]);
         }
         else
         {

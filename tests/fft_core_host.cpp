@@ -15,13 +15,17 @@
 template<typename T> struct C2 { T x, y; };
 template<typename T> struct InF
 {
+    struct Cursor { const C2<T>* p; int gs; };
     const C2<T>* src; int n;
-    C2<T> operator()(int line, int idx) const { return src[(size_t) line * n + idx]; }
+    Cursor cursor(int line, int idx0, int gs) const { return Cursor{src + (size_t) line * n + idx0, gs}; }
+    C2<T> load(const Cursor& c, int k) const { return c.p[k * c.gs]; }
 };
 template<typename T> struct OutF
 {
+    struct Cursor { C2<T>* p; int gs; };
     C2<T>* dst; int n;
-    void operator()(int line, int idx, C2<T> v) const { dst[(size_t) line * n + idx] = v; }
+    Cursor cursor(int line, int idx0, int gs) const { return Cursor{dst + (size_t) line * n + idx0, gs}; }
+    void store(const Cursor& c, int k, C2<T> v) const { c.p[k * c.gs] = v; }
 };
 template<typename T, int SGN, bool DIT> int run(int n, int maxr, int lshift,
         const int32_t* forced, const char* out)
