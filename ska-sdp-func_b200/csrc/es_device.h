@@ -108,6 +108,17 @@ int es_launch_correct(const EsGeom* g, void* dirty, const double* quad_kernel,
 int es_launch_plane_histogram(const EsGeom* g, const void* uvw,
         const void* freq, unsigned long long* hist, es_stream_t stream);
 
+/* ---- occupancy of the resident planes (es_scatter.cu) ----
+ * Per plane of a batch, es_occupancy_words(g) uint32 words:
+ *   [tu * nw + (tv >> 5)] bit (tv & 31): tile (tu, tv) has records on the plane
+ *   [ntile * nw + (tu >> 5)] bit (tu & 31): tile row tu has an occupied tile
+ * with nw = (ntile + 31) / 32. Unoccupied tiles of `planes` and unoccupied
+ * tile rows of the FFT intermediate are neither written nor read. */
+size_t es_occupancy_words(const EsGeom* g);
+int es_launch_occupancy(const EsGeom* g, const uint64_t* keys,
+        const uint32_t* tile_start, int first_plane, int nplanes,
+        uint32_t* occ, es_stream_t stream);
+
 /* ---- load-balanced work units (es_scatter.cu) ---- */
 
 size_t es_unit_bytes(void);                   /* bytes of one work unit */
@@ -146,26 +157,28 @@ void es_fft_destroy(EsFft* fft);
 /* Bytes of the transposed, pruned intermediate strip[plane][N][G]. */
 size_t es_fft_strip_bytes(const EsFft* fft, int nplanes);
 
-/* Gridding pass 1: planes[q][u][:] -> inverse FFT along v -> strip[q][v'][u]. */
+/* `occ` (all four passes): occupancy words of the batch, see above.
+ * Gridding pass 1: planes[q][u][:] -> inverse FFT along v -> strip[q][v'][u]. */
 int es_fft_grid_rows(const EsFft* fft, const void* planes, int nplanes,
-        void* strip, es_stream_t stream);
+        void* strip, const uint32_t* occ, es_stream_t stream);
 
 /* Gridding pass 2: strip[q][v'][:] -> inverse FFT along u -> w-screen ->
  * image_t[v'][u'] += sum over the nplanes planes (image_t is the transposed
  * dirty image, N x N reals). */
 int es_fft_grid_cols_screen(const EsFft* fft, const EsGeom* g,
         const void* strip, int first_plane, int nplanes, void* image_t,
-        es_stream_t stream);
+        const uint32_t* occ, es_stream_t stream);
 
 /* Degridding pass 1: image_t[v'][:] x conj w-screen, zero padded -> forward
  * FFT along u -> strip[q][v'][u]. */
 int es_fft_degrid_cols(const EsFft* fft, const EsGeom* g, const void* image_t,
-        int first_plane, int nplanes, void* strip, es_stream_t stream);
+        int first_plane, int nplanes, void* strip, const uint32_t* occ,
+        es_stream_t stream);
 
 /* Degridding pass 2: strip[q][:][u] zero padded -> forward FFT along v ->
  * planes[q][u][:]. */
 int es_fft_degrid_rows(const EsFft* fft, const void* strip, int nplanes,
-        void* planes, es_stream_t stream);
+        void* planes, const uint32_t* occ, es_stream_t stream);
 
 /* dst[r][c] = src[c][r] (add == 0) or dst[r][c] += src[c][r], n x n reals. */
 int es_launch_transpose(const void* src, void* dst, int n, int is_double,

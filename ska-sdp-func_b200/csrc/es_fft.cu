@@ -44,7 +44,7 @@
 #include "es_screen.h"
 
 #define ES_FFT_THREADS 512 /* upper bound of the CTA size (128 registers each) */
-#define ES_FFT_MAX_SMEM (227 * 1024)
+#define ES_FFT_MAX_SMEM (227 * 1024 - 64) /* 64 B of static occupancy words */
 
 /* CTA shape of one kernel family. */
 struct EsFftCfg
@@ -116,7 +116,18 @@ template<> struct Screen<double>
  * so a cursor is one pointer and one stride; WINDOW: indices outside
  * [k0, k0 + count) read as zero / are not stored (the pruning). */
 
-template<typename T2, bool WINDOW, bool ANY> struct LinearIn
+/* MASK: index idx (k0 == 0) belongs to 64-wide block idx >> 6; blocks whose
+ * bit in `bits` (shared memory) is clear read as zero / are not stored. */
+#define ES_FFT_OCC_WORDS 16 /* blocks <= 512: lines up to 32768 elements */
+static_assert(ES_TILE == 64, "occupancy blocks are addressed with idx >> 6");
+
+__device__ __forceinline__ bool occ_bit(const uint32_t* bits, int idx)
+{
+    const int t = idx >> 6;
+    return (bits[t >> 5] >> (t & 31)) & 1u;
+}
+
+template<typename T2, bool WINDOW, bool ANY, bool MASK = false> struct LinearIn
 {
     struct Cursor
     {
@@ -127,6 +138,7 @@ template<typename T2, bool WINDOW, bool ANY> struct LinearIn
     const T2* base;          /* element k0 of line 0 */
     ptrdiff_t estride, lstride;
     int k0, count;
+    const uint32_t* bits;    /* MASK */
     unsigned int any;        /* ANY: becomes non-zero when a loaded value is */
     __device__ __forceinline__ Cursor cursor(int line, int idx0, int gs) const
     {
@@ -141,14 +153,15 @@ template<typename T2, bool WINDOW, bool ANY> struct LinearIn
     {
         T2 v;
         v.x = 0; v.y = 0;
-        if (!WINDOW || (unsigned) (c.r0 + k * c.gs) < (unsigned) count)
+        if ((!WINDOW || (unsigned) (c.r0 + k * c.gs) < (unsigned) count) &&
+                (!MASK || occ_bit(bits, c.r0 + k * c.gs)))
             v = c.p[k * c.step];
         if (ANY) any |= (v.x != 0 || v.y != 0) ? 1u : 0u;
         return v;
     }
 };
 
-template<typename T2, bool WINDOW> struct LinearOut
+template<typename T2, bool WINDOW, bool MASK = false> struct LinearOut
 {
     struct Cursor
     {
@@ -159,6 +172,7 @@ template<typename T2, bool WINDOW> struct LinearOut
     T2* base;
     ptrdiff_t estride, lstride;
     int k0, count;
+    const uint32_t* bits;    /* MASK */
     __device__ __forceinline__ Cursor cursor(int line, int idx0, int gs) const
     {
         Cursor c;
@@ -170,7 +184,8 @@ template<typename T2, bool WINDOW> struct LinearOut
     }
     __device__ __forceinline__ void store(const Cursor& c, int k, const T2 v) const
     {
-        if (!WINDOW || (unsigned) (c.r0 + k * c.gs) < (unsigned) count)
+        if ((!WINDOW || (unsigned) (c.r0 + k * c.gs) < (unsigned) count) &&
+                (!MASK || occ_bit(bits, c.r0 + k * c.gs)))
             c.p[k * c.step] = v;
     }
 };
@@ -289,7 +304,30 @@ struct EsFftLayout
     int32_t lshift;    /* log2 of the columns per CTA of the column kernels */
     int32_t rows_pitch, cols_pitch;
     int64_t plane_elems; /* elements of T per plane (grid_size x image_size) */
+    int32_t ntile, occ_nw; /* occupancy words: es_device.h */
 };
+
+/* Words of plane q: tile bits of tile row tu at + tu * nw, the tile-row bits
+ * at + ntile * nw. */
+__device__ __forceinline__ const uint32_t* occ_plane(const uint32_t* occ,
+        const EsFftLayout& lay, int q)
+{
+    return occ + (size_t) q * (size_t) ((lay.ntile + 1) * lay.occ_nw);
+}
+
+/* Copies nw words to shared memory; true when any of them is non-zero
+ * (contains a barrier: every thread of the CTA must call it). */
+__device__ __forceinline__ bool occ_fetch(uint32_t* s_bits,
+        const uint32_t* src, int nw)
+{
+    uint32_t w = 0;
+    if ((int) threadIdx.x < nw)
+    {
+        w = src[threadIdx.x];
+        s_bits[threadIdx.x] = w;
+    }
+    return __syncthreads_or((int) (w != 0u)) != 0;
+}
 
 /* ------------------------------------------------------ gridding pass 1 */
 
@@ -299,15 +337,21 @@ __global__ void __launch_bounds__(ES_FFT_THREADS, 1) es_fft_grid_rows_kernel(
         const int32_t* __restrict__ bpos,
         const typename Cx<T>::T2* __restrict__ planes,
         typename Cx<T>::T2* __restrict__ strip, const int image_size,
-        const EsFftLayout lay)
+        const uint32_t* __restrict__ occ, const EsFftLayout lay)
 {
     typedef typename Cx<T>::T2 T2;
     extern __shared__ __align__(16) unsigned char es_fft_smem[];
+    __shared__ uint32_t s_bits[ES_FFT_OCC_WORDS];
     T2* x = (T2*) es_fft_smem;
     T2* tw = x + lay.rows_pitch;
     const int gsz = pl.n, n = image_size;
     const int u = blockIdx.x;
-    LinearIn<T2, false, true> in;
+    /* nothing was gridded onto this tile row: the column pass reads it as
+     * zeros without it being stored */
+    if (!occ_fetch(s_bits, occ_plane(occ, lay, blockIdx.y) +
+            (u >> 6) * lay.occ_nw, lay.occ_nw)) return;
+    LinearIn<T2, false, true, true> in;
+    in.bits = s_bits;
     in.base = planes + ((size_t) blockIdx.y * gsz + u) * gsz;
     in.estride = 1;
     in.lstride = 0;
@@ -359,15 +403,18 @@ es_fft_grid_cols_screen_kernel(const EsFftLine pl,
         const typename Cx<T>::T2* __restrict__ tw_g,
         const int32_t* __restrict__ bpos, const EsGeom g,
         const typename Cx<T>::T2* __restrict__ strip, const int first_plane,
-        const int nplanes, T* __restrict__ image_t, const EsFftLayout lay)
+        const int nplanes, T* __restrict__ image_t,
+        const uint32_t* __restrict__ occ, const EsFftLayout lay)
 {
     typedef typename Cx<T>::T2 T2;
     extern __shared__ __align__(16) unsigned char es_fft_smem[];
+    __shared__ uint32_t s_bits[ES_FFT_OCC_WORDS];
     T2* x = (T2*) es_fft_smem;
     T2* tw = x + ((size_t) lay.cols_pitch << lay.lshift);
     const int gsz = pl.n, n = g.image_size;
     const int col0 = blockIdx.x << lay.lshift;
-    LinearIn<T2, false, false> in;
+    LinearIn<T2, false, false, true> in;
+    in.bits = s_bits;
     in.estride = n;
     in.lstride = 1;
     in.k0 = 0;
@@ -386,6 +433,10 @@ es_fft_grid_cols_screen_kernel(const EsFftLine pl,
     for (int q = 0; q < nplanes; ++q)
     {
         __syncthreads(); /* twiddles loaded / previous plane's last pass done */
+        /* rows of unoccupied tile rows were not stored; an empty plane adds
+         * nothing */
+        if (!occ_fetch(s_bits, occ_plane(occ, lay, q) +
+                lay.ntile * lay.occ_nw, lay.occ_nw)) continue;
         in.base = strip + (size_t) q * lay.plane_elems + col0;
         out.w = (double) (first_plane + q) * g.inv_w_scale + g.min_plane_w;
         fft_all_passes<1, false, T>(x, pl, tw, bpos, lay.lshift, lay.cols_pitch,
@@ -401,15 +452,19 @@ __global__ void __launch_bounds__(ES_FFT_THREADS, 1) es_fft_degrid_cols_kernel(
         const int32_t* __restrict__ bpos, const EsGeom g,
         const T* __restrict__ image_t, const int first_plane,
         const int nplanes, typename Cx<T>::T2* __restrict__ strip,
-        const EsFftLayout lay)
+        const uint32_t* __restrict__ occ, const EsFftLayout lay)
 {
     typedef typename Cx<T>::T2 T2;
     extern __shared__ __align__(16) unsigned char es_fft_smem[];
+    __shared__ uint32_t s_bits[ES_FFT_OCC_WORDS];
     T2* x = (T2*) es_fft_smem;
     T2* tw = x + ((size_t) lay.cols_pitch << lay.lshift);
     const int gsz = pl.n, n = g.image_size;
     const int q = blockIdx.x % nplanes;
     const int col0 = (blockIdx.x / nplanes) << lay.lshift;
+    /* only the tile rows the gather reads are stored; none: nothing to do */
+    if (!occ_fetch(s_bits, occ_plane(occ, lay, q) + lay.ntile * lay.occ_nw,
+            lay.occ_nw)) return;
     ScreenIn<T, T2> in;
     in.image_t = image_t + (size_t) col0 * n + n / 2;
     in.n = n;
@@ -420,7 +475,8 @@ __global__ void __launch_bounds__(ES_FFT_THREADS, 1) es_fft_degrid_cols_kernel(
     in.pix2 = g.pixel_size * g.pixel_size;
     in.pix2f = (float) in.pix2;
     in.w = (double) (first_plane + q) * g.inv_w_scale + g.min_plane_w;
-    LinearOut<T2, false> out;
+    LinearOut<T2, false, true> out;
+    out.bits = s_bits;
     out.base = strip + (size_t) q * lay.plane_elems + col0;
     out.estride = n;
     out.lstride = 1;
@@ -440,14 +496,18 @@ __global__ void __launch_bounds__(ES_FFT_THREADS, 1) es_fft_degrid_rows_kernel(
         const int32_t* __restrict__ bpos,
         const typename Cx<T>::T2* __restrict__ strip,
         typename Cx<T>::T2* __restrict__ planes, const int image_size,
-        const EsFftLayout lay)
+        const uint32_t* __restrict__ occ, const EsFftLayout lay)
 {
     typedef typename Cx<T>::T2 T2;
     extern __shared__ __align__(16) unsigned char es_fft_smem[];
+    __shared__ uint32_t s_bits[ES_FFT_OCC_WORDS];
     T2* x = (T2*) es_fft_smem;
     T2* tw = x + lay.rows_pitch;
     const int gsz = pl.n, n = image_size;
     const int u = blockIdx.x;
+    /* only the tiles the gather reads are stored */
+    if (!occ_fetch(s_bits, occ_plane(occ, lay, blockIdx.y) +
+            (u >> 6) * lay.occ_nw, lay.occ_nw)) return;
     LinearIn<T2, true, false> in;
     in.base = strip + (size_t) blockIdx.y * lay.plane_elems + (size_t) u * n;
     in.estride = 1;
@@ -455,7 +515,8 @@ __global__ void __launch_bounds__(ES_FFT_THREADS, 1) es_fft_degrid_rows_kernel(
     in.k0 = gsz / 2 - n / 2;
     in.count = n;
     in.any = 0u;
-    LinearOut<T2, false> out;
+    LinearOut<T2, false, true> out;
+    out.bits = s_bits;
     out.base = planes + ((size_t) blockIdx.y * gsz + u) * gsz;
     out.estride = 1;
     out.lstride = 0;
@@ -544,6 +605,8 @@ EsFftLayout fft_layout(const EsFft* f)
     lay.rows_pitch = f->rows.pitch;
     lay.cols_pitch = f->cols.pitch;
     lay.plane_elems = f->plane_elems;
+    lay.ntile = (f->grid_size + ES_TILE - 1) / ES_TILE;
+    lay.occ_nw = (lay.ntile + 31) >> 5;
     return lay;
 }
 
@@ -586,7 +649,8 @@ int es_fft_create(int grid_size, int image_size, int is_double, EsFft** out)
     if (!bad && is_double)
         for (int i = 0; i < f->line.num_stages; ++i)
             if (f->line.stage[i].radix > ES_FFT_MAX_RADIX_DOUBLE) bad = 1;
-    if (bad || (grid_size & 1) || (image_size & 1) || image_size > grid_size)
+    if (bad || (grid_size & 1) || (image_size & 1) || image_size > grid_size ||
+            grid_size > ES_FFT_OCC_WORDS * 32 * ES_TILE)
     {
         free(f);
         return -1; /* unsupported size: caller falls back to cuFFT */
@@ -695,7 +759,7 @@ size_t es_fft_strip_bytes(const EsFft* f, int nplanes)
 }
 
 int es_fft_grid_rows(const EsFft* f, const void* planes, int nplanes,
-        void* strip, es_stream_t stream)
+        void* strip, const uint32_t* occ, es_stream_t stream)
 {
     cudaStream_t s = (cudaStream_t) stream;
     const EsFftLayout lay = fft_layout(f);
@@ -705,17 +769,18 @@ int es_fft_grid_rows(const EsFft* f, const void* planes, int nplanes,
         es_fft_grid_rows_kernel<double><<<grid, c.threads, c.smem_bytes,
                 s>>>(f->line, (const double2*) f->d_tw, f->d_bpos,
                 (const double2*) planes, (double2*) strip, f->image_size,
-                lay);
+                occ, lay);
     else
         es_fft_grid_rows_kernel<float><<<grid, c.threads, c.smem_bytes,
                 s>>>(f->line, (const float2*) f->d_tw, f->d_bpos,
                 (const float2*) planes, (float2*) strip, f->image_size,
-                lay);
+                occ, lay);
     return (int) cudaGetLastError();
 }
 
 int es_fft_grid_cols_screen(const EsFft* f, const EsGeom* g, const void* strip,
-        int first_plane, int nplanes, void* image_t, es_stream_t stream)
+        int first_plane, int nplanes, void* image_t, const uint32_t* occ,
+        es_stream_t stream)
 {
     cudaStream_t s = (cudaStream_t) stream;
     const EsFftLayout lay = fft_layout(f);
@@ -725,17 +790,18 @@ int es_fft_grid_cols_screen(const EsFft* f, const EsGeom* g, const void* strip,
         es_fft_grid_cols_screen_kernel<double><<<grid, c.threads,
                 c.smem_bytes, s>>>(f->line, (const double2*) f->d_tw,
                 f->d_bpos, *g, (const double2*) strip, first_plane, nplanes,
-                (double*) image_t, lay);
+                (double*) image_t, occ, lay);
     else
         es_fft_grid_cols_screen_kernel<float><<<grid, c.threads,
                 c.smem_bytes, s>>>(f->line, (const float2*) f->d_tw,
                 f->d_bpos, *g, (const float2*) strip, first_plane, nplanes,
-                (float*) image_t, lay);
+                (float*) image_t, occ, lay);
     return (int) cudaGetLastError();
 }
 
 int es_fft_degrid_cols(const EsFft* f, const EsGeom* g, const void* image_t,
-        int first_plane, int nplanes, void* strip, es_stream_t stream)
+        int first_plane, int nplanes, void* strip, const uint32_t* occ,
+        es_stream_t stream)
 {
     cudaStream_t s = (cudaStream_t) stream;
     const EsFftLayout lay = fft_layout(f);
@@ -745,17 +811,17 @@ int es_fft_degrid_cols(const EsFft* f, const EsGeom* g, const void* image_t,
         es_fft_degrid_cols_kernel<double><<<grid, c.threads, c.smem_bytes,
                 s>>>(f->line, (const double2*) f->d_tw, f->d_bpos, *g,
                 (const double*) image_t, first_plane, nplanes,
-                (double2*) strip, lay);
+                (double2*) strip, occ, lay);
     else
         es_fft_degrid_cols_kernel<float><<<grid, c.threads, c.smem_bytes,
                 s>>>(f->line, (const float2*) f->d_tw, f->d_bpos, *g,
                 (const float*) image_t, first_plane, nplanes,
-                (float2*) strip, lay);
+                (float2*) strip, occ, lay);
     return (int) cudaGetLastError();
 }
 
 int es_fft_degrid_rows(const EsFft* f, const void* strip, int nplanes,
-        void* planes, es_stream_t stream)
+        void* planes, const uint32_t* occ, es_stream_t stream)
 {
     cudaStream_t s = (cudaStream_t) stream;
     const EsFftLayout lay = fft_layout(f);
@@ -765,12 +831,12 @@ int es_fft_degrid_rows(const EsFft* f, const void* strip, int nplanes,
         es_fft_degrid_rows_kernel<double><<<grid, c.threads, c.smem_bytes,
                 s>>>(f->line, (const double2*) f->d_tw, f->d_bpos,
                 (const double2*) strip, (double2*) planes, f->image_size,
-                lay);
+                occ, lay);
     else
         es_fft_degrid_rows_kernel<float><<<grid, c.threads, c.smem_bytes,
                 s>>>(f->line, (const float2*) f->d_tw, f->d_bpos,
                 (const float2*) strip, (float2*) planes, f->image_size,
-                lay);
+                occ, lay);
     return (int) cudaGetLastError();
 }
 

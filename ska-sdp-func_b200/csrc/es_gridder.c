@@ -71,6 +71,7 @@ struct sdp_GridderUvwEsFft
 
     /* load-balanced work units of the current plane batch */
     EsBuffer units, unit_counters, split_done, partials;
+    EsBuffer occ;     /* plane_batch x es_occupancy_words: occupied tiles / tile rows */
 
     /* staging for host arrays */
     EsBuffer st_uvw, st_freq, st_vis, st_weight, st_dirty;
@@ -320,6 +321,7 @@ void sdp_gridder_uvw_es_fft_free_plan(sdp_GridderUvwEsFft* plan)
         &plan->keys_a, &plan->keys_b, &plan->vals_a, &plan->vals_b,
         &plan->records, &plan->tile_start, &plan->sort_temp, &plan->acc,
         &plan->units, &plan->unit_counters, &plan->split_done, &plan->partials,
+        &plan->occ,
         &plan->st_uvw, &plan->st_freq, &plan->st_vis, &plan->st_weight,
         &plan->st_dirty
     };
@@ -507,6 +509,8 @@ sdp_GridderUvwEsFft* sdp_gridder_uvw_es_fft_create_plan(
                 buffer_reserve(&plan->image_t, real_bytes(plan) *
                         (size_t) image_size * (size_t) image_size,
                         &try_status);
+                buffer_reserve(&plan->occ, (size_t) plan->plane_batch *
+                        es_occupancy_words(g) * sizeof(uint32_t), &try_status);
             }
             if (!try_status) break;
             buffer_free(&plan->planes);
@@ -992,10 +996,15 @@ void sdp_grid_uvw_es_fft(sdp_GridderUvwEsFft* plan, const sdp_Mem* uvw,
         int nb = g->plane_end - first;
         if (nb > plan->plane_batch) nb = plan->plane_batch;
         stage_mark(plan);
+        /* pruned mode: only occupied tiles are written / transformed */
+        if (plan->pruned_fft)
+            ES_CUDA(es_launch_occupancy(g, (const uint64_t*) plan->keys_b.ptr,
+                    (const uint32_t*) plan->tile_start.ptr, first, nb,
+                    (uint32_t*) plan->occ.ptr, s));
         ES_CUDA(es_launch_work_plan(g, (const uint64_t*) plan->keys_b.ptr,
                 (const uint32_t*) plan->tile_start.ptr, first, nb, 1,
                 lim.split, lim.max_units, ES_MAX_SPLIT_ITEMS, lim.max_partials,
-                0, plan->units.ptr, (uint32_t*) plan->unit_counters.ptr,
+                plan->pruned_fft ? 1 : 0, plan->units.ptr, (uint32_t*) plan->unit_counters.ptr,
                 (uint32_t*) plan->split_done.ptr, s));
         ES_CUDA(es_launch_scatter2(g, plan->records.ptr, plan->units.ptr,
                 (uint32_t*) plan->unit_counters.ptr, first, plan->planes.ptr,
@@ -1007,10 +1016,11 @@ void sdp_grid_uvw_es_fft(sdp_GridderUvwEsFft* plan, const sdp_Mem* uvw,
             /* inverse transform (es_fft.cpp:568) as two pruned line passes,
              * the second fused with the w-screen and the plane sum */
             ES_CUDA(es_fft_grid_rows(plan->pruned_fft, plan->planes.ptr, nb,
-                    plan->strip.ptr, s));
+                    plan->strip.ptr, (const uint32_t*) plan->occ.ptr, s));
             stage_mark(plan);
             ES_CUDA(es_fft_grid_cols_screen(plan->pruned_fft, g,
-                    plan->strip.ptr, first, nb, plan->image_t.ptr, s));
+                    plan->strip.ptr, first, nb, plan->image_t.ptr,
+                    (const uint32_t*) plan->occ.ptr, s));
             plan->stats.kernel_launches += 1;
         }
         else
@@ -1106,11 +1116,16 @@ void sdp_ifft_degrid_uvw_es(sdp_GridderUvwEsFft* plan, const sdp_Mem* uvw,
         stage_mark(plan);
         if (plan->pruned_fft)
         {
+            /* only the tiles the gather reads are produced */
+            ES_CUDA(es_launch_occupancy(g, (const uint64_t*) plan->keys_b.ptr,
+                    (const uint32_t*) plan->tile_start.ptr, first, nb,
+                    (uint32_t*) plan->occ.ptr, s));
             ES_CUDA(es_fft_degrid_cols(plan->pruned_fft, g,
-                    plan->image_t.ptr, first, nb, plan->strip.ptr, s));
+                    plan->image_t.ptr, first, nb, plan->strip.ptr,
+                    (const uint32_t*) plan->occ.ptr, s));
             stage_mark(plan);
             ES_CUDA(es_fft_degrid_rows(plan->pruned_fft, plan->strip.ptr, nb,
-                    plan->planes.ptr, s));
+                    plan->planes.ptr, (const uint32_t*) plan->occ.ptr, s));
         }
         else
         {

@@ -124,6 +124,34 @@ __global__ void __launch_bounds__(256) es_work_plan_kernel(EsGeom g,
     }
 }
 
+/* ----------------------------------------------------------- occupancy */
+
+/* One thread per (uv tile, w-plane) of the batch: sets the bit of every pair
+ * that has records (layout: es_device.h, es_occupancy_words). Everything
+ * downstream moves only occupied tiles / tile rows: the scatter writes them,
+ * the line FFTs read (gridding) or store (degridding) them, the gather reads
+ * them. Real coverage is sparse per plane (SKA-Low snapshot: < 0.3 % of the
+ * tiles, 0.5 .. 50 % of the tile rows). */
+__global__ void __launch_bounds__(256) es_occupancy_kernel(EsGeom g,
+        const uint64_t* __restrict__ keys,
+        const uint32_t* __restrict__ tile_start, int first_plane, int nplanes,
+        uint32_t* __restrict__ occ)
+{
+    const int ntiles = g.ntile * g.ntile;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= ntiles * nplanes) return;
+    const int q = i / ntiles, tile = i - q * ntiles;
+    uint32_t a, b;
+    es_entry_range(g, keys, tile_start, tile, first_plane + q, first_plane + q,
+            a, b);
+    if (a == b) return;
+    const int tu = tile / g.ntile, tv = tile - tu * g.ntile;
+    const int nw = (g.ntile + 31) >> 5;
+    uint32_t* o = occ + (size_t) q * (size_t) ((g.ntile + 1) * nw);
+    atomicOr(&o[tu * nw + (tv >> 5)], 1u << (tv & 31));
+    atomicOr(&o[g.ntile * nw + (tu >> 5)], 1u << (tu & 31));
+}
+
 /* ------------------------------------------------------------- scatter */
 
 #define ES_SC_THREADS 128
@@ -349,6 +377,25 @@ size_t es_unit_bytes(void)
 size_t es_partial_tile_bytes(int is_double)
 {
     return (size_t) ES_TILE * ES_TILE * (is_double ? 16 : 8);
+}
+
+size_t es_occupancy_words(const EsGeom* g)
+{
+    return (size_t) (g->ntile + 1) * (size_t) ((g->ntile + 31) >> 5);
+}
+
+int es_launch_occupancy(const EsGeom* g, const uint64_t* keys,
+        const uint32_t* tile_start, int first_plane, int nplanes,
+        uint32_t* occ, es_stream_t stream)
+{
+    cudaStream_t s = (cudaStream_t) stream;
+    cudaError_t err = cudaMemsetAsync(occ, 0, (size_t) nplanes *
+            es_occupancy_words(g) * sizeof(uint32_t), s);
+    if (err != cudaSuccess) return (int) err;
+    const int nitems = g->ntile * g->ntile * nplanes;
+    es_occupancy_kernel<<<(nitems + 255) / 256, 256, 0, s>>>(*g, keys,
+            tile_start, first_plane, nplanes, occ);
+    return (int) cudaGetLastError();
 }
 
 int es_launch_work_plan(const EsGeom* g, const uint64_t* keys,
