@@ -276,7 +276,7 @@ def run_reference_arm(args):
                 "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    emit_json(line)
 
 
 # ------------------------------------------------------------ product arm
@@ -564,9 +564,22 @@ def run_product_arm(args):
         "roofline": roofline, "roofline_call": roofline_call, "stages": stages,
         "cpu_baseline": cpu,
     }
-    print(json.dumps(line))
+    emit_json(line)
     if world > 1:
         dist.destroy_process_group()
+
+
+_JSON_FD = None
+
+
+def emit_json(line):
+    text = json.dumps(line) + "\n"
+    sys.stdout.flush()
+    if _JSON_FD is None:
+        sys.stdout.write(text)
+        sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, text.encode())
 
 
 def main():
@@ -581,6 +594,12 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+    # stdout carries exactly ONE line, the JSON: anything libraries print there
+    # (NCCL's version banner under torchrun) is sent to stderr instead
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference_arm(args)
     else:

@@ -439,8 +439,13 @@ es_fft_grid_cols_screen_kernel(const EsFftLine pl,
                 lay.ntile * lay.occ_nw, lay.occ_nw)) continue;
         in.base = strip + (size_t) q * lay.plane_elems + col0;
         out.w = (double) (first_plane + q) * g.inv_w_scale + g.min_plane_w;
-        fft_all_passes<1, false, T>(x, pl, tw, bpos, lay.lshift, lay.cols_pitch,
-                in, out);
+        for (int step = 0; step < pl.num_stages; ++step)
+        {
+            if (step > 0) __syncthreads();
+            es_line_pass<1, false, T>(x, pl, step, tw, bpos, lay.lshift,
+                    lay.cols_pitch, (int) threadIdx.x, (int) blockDim.x, in,
+                    out);
+        }
     }
 }
 

@@ -270,13 +270,35 @@ __global__ void __launch_bounds__(ES_SC_THREADS) es_scatter2_kernel(EsGeom g,
                 if (lane_active && col >= 0 && col < cols_valid)
                 {
                     const T pre = s_kre[e * NS + c], pim = s_kim[e * NS + c];
-                    for (int r = r_lo + rsub; r <= r_hi; r += rps)
+                    /* footprint rows of this lane, MS at a time: all loads,
+                     * then all updates, then all stores (distinct cells), so
+                     * the shared-memory round trip is paid once per record */
+                    constexpr int MS = (NS <= 9) ? 3 : 4;
+                    for (int rb = r_lo + rsub; rb <= r_hi; rb += MS * rps)
                     {
-                        const T ku = s_ku[e * NS + (r - lu0)];
-                        T2 cell = tile[r * ES_TILE + col];
-                        cell.x += pre * ku;
-                        cell.y += pim * ku;
-                        tile[r * ES_TILE + col] = cell;
+                        T2 cell[MS];
+                        T ku[MS];
+#pragma unroll
+                        for (int m = 0; m < MS; ++m)
+                        {
+                            const int r = rb + m * rps;
+                            if (r <= r_hi)
+                            {
+                                ku[m] = s_ku[e * NS + (r - lu0)];
+                                cell[m] = tile[r * ES_TILE + col];
+                            }
+                        }
+#pragma unroll
+                        for (int m = 0; m < MS; ++m)
+                        {
+                            const int r = rb + m * rps;
+                            if (r <= r_hi)
+                            {
+                                cell[m].x += pre * ku[m];
+                                cell[m].y += pim * ku[m];
+                                tile[r * ES_TILE + col] = cell[m];
+                            }
+                        }
                     }
                 }
             }

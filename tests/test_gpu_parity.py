@@ -11,8 +11,9 @@ import numpy as np
 import pytest
 
 from tests import synth
-from tests.helpers import (TOL, check_parity, product_degrid, product_grid,
-                           rel_max)
+from ska_sdp_func.grid_data import GridderUvwEsFft
+from tests.helpers import (TOL, check_parity, oracle_degrid, oracle_grid,
+                           product_degrid, product_grid, rel_max)
 
 pytestmark = pytest.mark.gpu
 
@@ -230,3 +231,36 @@ def test_plane_partition_sums_to_full_result():
 
 def test_parity_tolerances_are_the_stated_ones():
     assert TOL[np.dtype(np.float32)] == 1e-5 and TOL[np.dtype(np.float64)] == 1e-10
+
+
+@pytest.mark.parametrize("single", [True, False])
+def test_sparse_coverage_after_dense_call_on_the_same_plan(single):
+    """Only occupied uv tiles / tile rows of the resident w-planes are written
+    and transformed (es_scatter.cu: es_occupancy_kernel, es_fft.cu masks). A
+    plan's buffers therefore still hold the previous call's cells wherever the
+    next call has no visibilities: grid a dense set, then a sparse, differently
+    placed one on the SAME plan, and both directions must still match the
+    oracle on the sparse set."""
+    import copy
+    n = 768
+    dense = synth.uniform_box(300, 16, n, fov_deg=3.0, single=single)
+    sparse = copy.deepcopy(dense)
+    # keep the rows that fix the w range (so both plans share one w lattice)
+    # plus three more; all other rows collapse onto one kept position
+    aw = np.abs(dense["uvw"][:, 2])
+    keep = np.unique(np.concatenate([[np.argmin(aw), np.argmax(aw)],
+                                     [17, 101, 233]]))
+    far = np.setdiff1d(np.arange(dense["uvw"].shape[0]), keep)
+    sparse["uvw"][far] = sparse["uvw"][keep[0]]
+    tol = TOL[np.dtype(dense["uvw"].dtype)]
+    eps = 1e-5 if single else 1e-9
+    assert GridderUvwEsFft.get_w_range(dense["uvw"], dense["freq_hz"]) == \
+        GridderUvwEsFft.get_w_range(sparse["uvw"], sparse["freq_hz"])
+    d1, g = product_grid(dense, eps, True)
+    product_degrid(dense, eps, True, g)
+    assert rel_max(d1, oracle_grid(dense, eps, True)) <= tol
+    # sparse call on the same plan: its buffers hold the dense call's cells
+    d2, _ = product_grid(sparse, eps, True, g)
+    v2, _, _ = product_degrid(sparse, eps, True, g)
+    assert rel_max(d2, oracle_grid(sparse, eps, True)) <= tol
+    assert rel_max(v2, oracle_degrid(sparse, eps, True)[0]) <= tol
