@@ -63,6 +63,11 @@ WORKLOADS = {
                make=lambda seed: synth.reference_test_case(256, seed=40 + seed),
                eps=1e-5, wstack=True),
     # BASELINE.json configs[3]
+    "C3": dict(desc="degrid (predict) from 8192^2 model image, 15500 rows x 1024 "
+                    "channels (1.6e7 vis), Mid-like uvw, fp64, eps=1e-10 "
+                    "(BASELINE.json configs[2])",
+               make=lambda seed: synth.mid_like_predict(seed=42 + seed),
+               eps=1e-10, wstack=True),
     "C4": dict(desc="SKA-Low AA*-like snapshot: 130816 baselines x 1024 channels, "
                     "16384^2 image, fp32, eps=1e-5 (BASELINE.json configs[3])",
                make=lambda seed: synth.ska_low_snapshot(512, 1024, 16384,
@@ -493,8 +498,8 @@ def run_product_arm(args):
     launches_dom = batches
     dom = stages[dominant]
     roofline = {
-        "kernel": {"scatter": "es_scatter_kernel", "apply_screen": "es_apply_screen_kernel",
-                   "gather": "es_gather_kernel",
+        "kernel": {"scatter": "es_scatter2_kernel", "apply_screen": "es_apply_screen_kernel",
+                   "gather": "es_gather2_kernel",
                    "reverse_screen": "es_reverse_screen_kernel",
                    "fft_rows": "es_fft_degrid_rows_kernel" if degrid
                                else "es_fft_grid_rows_kernel",

@@ -8,20 +8,16 @@ import sys
 
 KEYS = [
     "gpu__time_duration.sum", "dram__bytes_read.sum ", "dram__bytes_write.sum ",
-    "dram__throughput.avg.pct_of_peak_sustained_elapsed",
-    "lts__t_bytes.sum ", "l1tex__t_bytes.sum ",
-    "sm__throughput.avg.pct_of_peak_sustained_elapsed",
+    "lts__t_bytes.sum ", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
     "sm__warps_active.avg.pct_of_peak_sustained_active",
-    "launch__registers_per_thread", "launch__occupancy_limit",
-    "launch__block_size", "launch__grid_size", "launch__waves_per_multiprocessor",
-    "smsp__average_warp", "smsp__issue_active.avg.pct",
-    "sm__inst_executed_pipe_fma", "sm__pipe_fma_cycles_active.avg.pct",
-    "sm__inst_executed_pipe_lsu", "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum",
+    "launch__registers_per_thread ", "launch__block_size", "launch__grid_size",
+    "launch__occupancy_limit_shared_mem", "launch__occupancy_limit_registers",
+    "smsp__issue_active.avg.pct", "smsp__inst_executed.sum ",
+    "sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active",
+    "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active",
+    "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum ",
     "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum ",
-    "smsp__pcsamp_warps_issue_stalled",
-    "l1tex__t_sectors_pipe_lsu_mem_global_op_ld.sum ", "l1tex__t_requests_pipe_lsu_mem_global_op_ld.sum ",
-    "l1tex__t_sectors_pipe_lsu_mem_global_op_st.sum ", "l1tex__t_requests_pipe_lsu_mem_global_op_st.sum ",
-    "lts__t_sector_hit_rate.pct",
+    "smsp__pcsamp_warps_issue_stalled", "lts__t_sector_hit_rate.pct",
 ]
 
 
@@ -38,7 +34,7 @@ def main():
         stalls = []
         for i, h in enumerate(hdr):
             hh = h + " "
-            if any(hh.startswith(k) or k.strip() in h for k in KEYS + extra):
+            if any(hh.startswith(k) for k in KEYS) or any(k in h for k in extra):
                 if "pcsamp_warps_issue_stalled" in h:
                     try:
                         stalls.append((float(r[i].replace(",", "")), h.replace("smsp__pcsamp_warps_issue_stalled_", "")))

@@ -100,6 +100,24 @@ __device__ __forceinline__ void es_entry_range(const EsGeom& g,
     b = l;
 }
 
+/* ------------------------------------------------------- work units */
+
+/* One unit of the load-balanced work lists (es_scatter.cu: es_work_plan_kernel). */
+struct __align__(16) EsUnit
+{
+    uint32_t a, b;        /* record range of this slice */
+    int32_t tile;         /* tile index tu * ntile + tv */
+    int32_t plane_q;      /* plane within the batch */
+    int32_t num_slices;   /* K: 1 = unsplit */
+    int32_t slice;        /* 0 .. K-1 */
+    int32_t split_slot;   /* index of the completion counter (K > 1) */
+    uint32_t partial_base; /* first partial tile in scratch (K > 1) */
+};
+
+static_assert(sizeof(EsUnit) == 32, "work unit must be 32 bytes");
+
+enum { CTR_UNITS = 0, CTR_SPLIT = 1, CTR_PARTIALS = 2, CTR_NEXT = 3 };
+
 } // namespace es
 
 #endif

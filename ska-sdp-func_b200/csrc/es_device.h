@@ -142,6 +142,12 @@ int es_launch_scatter2(const EsGeom* g, const void* records, const void* units,
         uint32_t* counters, int first_plane, void* planes, void* scratch,
         uint32_t* split_done, es_stream_t stream);
 
+/* Degridding: persistent CTAs execute the units of a per_plane == 0 work
+ * list (one record belongs to exactly one unit). */
+int es_launch_gather2(const EsGeom* g, const void* records, const void* units,
+        uint32_t* counters, int first_plane, int nplanes, const void* planes,
+        void* acc, es_stream_t stream);
+
 /* ---- pruned w-plane FFT with fused w-screen (es_fft.cu) ---- */
 
 typedef struct EsFft EsFft;

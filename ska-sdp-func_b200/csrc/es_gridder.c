@@ -1091,6 +1091,9 @@ void sdp_ifft_degrid_uvw_es(sdp_GridderUvwEsFft* plan, const sdp_Mem* uvw,
     buffer_reserve(&plan->acc, (size_t) (m > 0 ? m : 1) * cplx, status);
     if (*status) return;
     ES_CUDA(cudaMemsetAsync(plan->acc.ptr, 0, (size_t) (m > 0 ? m : 1) * cplx, s));
+    EsWorkLimits glim;
+    work_reserve(plan, 1, m, 0, &glim, status);
+    if (*status) return;
     event_mark(plan, 1);
 
     /* grid correction in place on the caller's image (es_fft.cpp:789-825) */
@@ -1136,9 +1139,13 @@ void sdp_ifft_degrid_uvw_es(sdp_GridderUvwEsFft* plan, const sdp_Mem* uvw,
             if (*status) return;
         }
         stage_mark(plan);
-        ES_CUDA(es_launch_gather(g, plan->records.ptr,
-                (const uint64_t*) plan->keys_b.ptr,
-                (const uint32_t*) plan->tile_start.ptr, first, nb,
+        /* (tile, record slice) units: heavy tiles are shared by many CTAs */
+        ES_CUDA(es_launch_work_plan(g, (const uint64_t*) plan->keys_b.ptr,
+                (const uint32_t*) plan->tile_start.ptr, first, nb, 0,
+                glim.split, glim.max_units, 0, 0, 1, plan->units.ptr,
+                (uint32_t*) plan->unit_counters.ptr, 0, s));
+        ES_CUDA(es_launch_gather2(g, plan->records.ptr, plan->units.ptr,
+                (uint32_t*) plan->unit_counters.ptr, first, nb,
                 plan->planes.ptr, plan->acc.ptr, s));
         stage_mark(plan);
         plan->stats.kernel_launches += 3;

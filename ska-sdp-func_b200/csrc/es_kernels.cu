@@ -351,21 +351,17 @@ __global__ void __launch_bounds__(ES_SCATTER_THREADS) es_scatter_kernel(
  * once, and its accumulator gets one read-modify-write (owned by exactly one
  * thread, so no atomics and a deterministic sum).
  * NS: footprint slots per axis handled (support + 1 <= NS). */
+/* Records [a, b) of one tile: acc[e] += sum over the planes of the batch and
+ * the footprint cells of plane * kernel (kernels.cu:201-268, solving = 0). */
 template<typename T, int NS>
-__global__ void __launch_bounds__(ES_GATHER_THREADS) es_gather_kernel(
-        EsGeom g, const typename Prec<T>::Rec* __restrict__ records,
-        const uint64_t* __restrict__ keys,
-        const uint32_t* __restrict__ tile_start, int first_plane, int nplanes,
-        const typename Prec<T>::T2* __restrict__ planes,
+__device__ __forceinline__ void es_gather_range(const EsGeom& g,
+        const typename Prec<T>::Rec* __restrict__ records, const int tile_id,
+        const uint32_t a, const uint32_t b, const int first_plane,
+        const int nplanes, const typename Prec<T>::T2* __restrict__ planes,
         typename Prec<T>::T2* __restrict__ acc)
 {
     typedef typename Prec<T>::T2 T2;
     typedef typename Prec<T>::Rec Rec;
-    const int tile_id = blockIdx.x;
-    uint32_t a, b;
-    es_entry_range(g, keys, tile_start, tile_id, first_plane,
-            first_plane + nplanes - 1, a, b);
-    if (a == b) return;
     const int tu = tile_id / g.ntile, tv = tile_id % g.ntile;
     const int gsz = g.grid_size;
     const size_t plane_cells = (size_t) gsz * gsz;
@@ -433,6 +429,52 @@ __global__ void __launch_bounds__(ES_GATHER_THREADS) es_gather_kernel(
         t.x += sum_re;
         t.y += sum_im;
         acc[e] = t;
+    }
+}
+
+/* One CTA per uv tile (cuFFT fallback path). */
+template<typename T, int NS>
+__global__ void __launch_bounds__(ES_GATHER_THREADS) es_gather_kernel(
+        EsGeom g, const typename Prec<T>::Rec* __restrict__ records,
+        const uint64_t* __restrict__ keys,
+        const uint32_t* __restrict__ tile_start, int first_plane, int nplanes,
+        const typename Prec<T>::T2* __restrict__ planes,
+        typename Prec<T>::T2* __restrict__ acc)
+{
+    const int tile_id = blockIdx.x;
+    uint32_t a, b;
+    es_entry_range(g, keys, tile_start, tile_id, first_plane,
+            first_plane + nplanes - 1, a, b);
+    if (a == b) return;
+    es_gather_range<T, NS>(g, records, tile_id, a, b, first_plane, nplanes,
+            planes, acc);
+}
+
+/* Load-balanced form: persistent CTAs pull (tile, record slice) units from
+ * the list of es_work_plan_kernel (per_plane = 0). Real uv coverage is very
+ * uneven (a Mid- or Low-like core puts ~10 % of all records into one tile):
+ * with one CTA per tile a single SM does most of the call. A record belongs
+ * to exactly one unit, so acc[e] has one writer. */
+template<typename T, int NS>
+__global__ void __launch_bounds__(ES_GATHER_THREADS) es_gather2_kernel(
+        EsGeom g, const typename Prec<T>::Rec* __restrict__ records,
+        const EsUnit* __restrict__ units, uint32_t* __restrict__ counters,
+        int first_plane, int nplanes,
+        const typename Prec<T>::T2* __restrict__ planes,
+        typename Prec<T>::T2* __restrict__ acc)
+{
+    __shared__ uint32_t s_work;
+    const uint32_t num_units = counters[CTR_UNITS];
+    for (;;)
+    {
+        __syncthreads();
+        if (threadIdx.x == 0) s_work = atomicAdd(&counters[CTR_NEXT], 1u);
+        __syncthreads();
+        const uint32_t w = s_work;
+        if (w >= num_units) break;
+        const EsUnit u = units[w];
+        es_gather_range<T, NS>(g, records, u.tile, u.a, u.b, first_plane,
+                nplanes, planes, acc);
     }
 }
 
@@ -672,6 +714,32 @@ static int launch_scatter_t(const EsGeom* g, const void* records,
     return (int) cudaGetLastError();
 }
 
+template<typename T, int NS>
+static int launch_gather2_ts(const EsGeom* g, const void* records,
+        const void* units, uint32_t* counters, int first_plane, int nplanes,
+        const void* planes, void* acc, cudaStream_t s)
+{
+    typedef typename Prec<T>::T2 T2;
+    typedef typename Prec<T>::Rec Rec;
+    static int grid_size = 0;
+    if (grid_size == 0)
+    {
+        int dev = 0, sms = 0, per_sm = 0;
+        cudaError_t err = cudaGetDevice(&dev);
+        if (err == cudaSuccess) err = cudaDeviceGetAttribute(&sms,
+                cudaDevAttrMultiProcessorCount, dev);
+        if (err == cudaSuccess) err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(
+                &per_sm, es_gather2_kernel<T, NS>, ES_GATHER_THREADS, 0);
+        if (err != cudaSuccess) return (int) err;
+        if (per_sm < 1) per_sm = 1;
+        grid_size = sms * per_sm;
+    }
+    es_gather2_kernel<T, NS><<<grid_size, ES_GATHER_THREADS, 0, s>>>(*g,
+            (const Rec*) records, (const EsUnit*) units, counters, first_plane,
+            nplanes, (const T2*) planes, (T2*) acc);
+    return (int) cudaGetLastError();
+}
+
 template<typename T>
 static int launch_gather_t(const EsGeom* g, const void* records,
         const uint64_t* keys, const uint32_t* tile_start, int first_plane,
@@ -855,6 +923,25 @@ int es_launch_gather(const EsGeom* g, const void* records,
         launch_gather_t<double>(g, records, keys, tile_start, first_plane,
                 nplanes, planes, acc, s) :
         launch_gather_t<float>(g, records, keys, tile_start, first_plane,
+                nplanes, planes, acc, s);
+}
+
+int es_launch_gather2(const EsGeom* g, const void* records, const void* units,
+        uint32_t* counters, int first_plane, int nplanes, const void* planes,
+        void* acc, es_stream_t stream)
+{
+    cudaStream_t s = (cudaStream_t) stream;
+    const bool wide = g->support + 1 > 9;
+    if (g->is_double)
+        return wide ?
+            launch_gather2_ts<double, 17>(g, records, units, counters,
+                    first_plane, nplanes, planes, acc, s) :
+            launch_gather2_ts<double, 9>(g, records, units, counters,
+                    first_plane, nplanes, planes, acc, s);
+    return wide ?
+        launch_gather2_ts<float, 17>(g, records, units, counters, first_plane,
+                nplanes, planes, acc, s) :
+        launch_gather2_ts<float, 9>(g, records, units, counters, first_plane,
                 nplanes, planes, acc, s);
 }
 

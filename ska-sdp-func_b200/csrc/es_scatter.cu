@@ -37,21 +37,6 @@ using namespace es;
 
 namespace {
 
-struct __align__(16) EsUnit
-{
-    uint32_t a, b;        /* record range of this slice */
-    int32_t tile;         /* tile index tu * ntile + tv */
-    int32_t plane_q;      /* plane within the batch */
-    int32_t num_slices;   /* K: 1 = unsplit */
-    int32_t slice;        /* 0 .. K-1 */
-    int32_t split_slot;   /* index of the completion counter (K > 1) */
-    uint32_t partial_base; /* first partial tile in scratch (K > 1) */
-};
-
-static_assert(sizeof(EsUnit) == 32, "work unit must be 32 bytes");
-
-enum { CTR_UNITS = 0, CTR_SPLIT = 1, CTR_PARTIALS = 2, CTR_NEXT = 3 };
-
 /* per_plane != 0: one item per (tile, plane); else one item per tile covering
  * the whole plane range (gather side). */
 __global__ void __launch_bounds__(256) es_work_plan_kernel(EsGeom g,
