@@ -388,17 +388,28 @@ def run_product_arm(args):
     value = world * n_vis / (ms_per_step * 1e-3) / 1e6
 
     # ---- e2e: the same call with HOST arrays (copies inside the timed region)
+    e2e_steps = max(2, min(args.steps, 5))
     if world == 1:
         a_uvw, a_freq = h_uvw.numpy(), h_freq.numpy()
         a_vis, a_wgt, a_img = h_vis.numpy(), h_wgt.numpy(), h_img.numpy()
+        # Nothing but the product call is inside the timed region: gridding
+        # accumulates into the caller's image (+=, part of the contract), so
+        # the same host image is simply reused; degridding corrects the
+        # caller's image in place, so every step gets its own pinned copy of
+        # the model image, prepared before the clock starts.
+        step_imgs = []
+        if degrid:
+            for _ in range(e2e_steps + 1):
+                t_img = h_img0.clone().pin_memory()
+                step_imgs.append(t_img.numpy())
+        step_no = [0]
 
         def host_step():
             if degrid:
-                a_img[...] = h_img0.numpy()
-                a_vis[...] = 0
-                gridder.ifft_grid_uvw_es(a_uvw, a_freq, a_vis, a_wgt, a_img)
+                img_k = step_imgs[step_no[0] % len(step_imgs)]
+                step_no[0] += 1
+                gridder.ifft_grid_uvw_es(a_uvw, a_freq, a_vis, a_wgt, img_k)
             else:
-                a_img[...] = 0
                 gridder.grid_uvw_es_fft(a_uvw, a_freq, a_vis, a_wgt, a_img)
     else:
         def host_step():
@@ -410,7 +421,6 @@ def run_product_arm(args):
             device_step()
             h_img.copy_(d_img, non_blocking=True)
             torch.cuda.synchronize()
-    e2e_steps = max(2, min(args.steps, 5))
     host_step()
     fence()
     t0 = time.perf_counter()
@@ -507,10 +517,22 @@ def run_product_arm(args):
                                       else "es_fft_grid_cols_screen_kernel"}[dominant],
         "bound": "hbm", "achieved": dom["GB/s"], "peak": peak, "unit": "GB/s",
         "frac": dom["frac"], "traffic": None, "peak_source": peak_src,
+        "bound_note": "HBM is the contract's roofline; ncu shows the line-FFT "
+                      "kernels limited by instruction issue (see profiles/README.md)",
         "launches_per_step": launches_dom,
         "algorithmic_bytes_per_launch": stage_bytes[dominant] / launches_dom,
         "avg_launch_ms": stage_ms[dominant] / launches_dom,
     }
+    # measured DRAM bytes per launch of this kernel on this workload, from the
+    # committed `ncu --set full` capture (profiles/r01_traffic.json)
+    try:
+        with open(os.path.join(ROOT, "profiles", "r01_traffic.json")) as f:
+            tr = json.load(f).get(args.workload, {}).get(roofline["kernel"])
+        if tr:
+            roofline["traffic"] = tr["dram_bytes_per_launch"]
+            roofline["traffic_source"] = tr["source"]
+    except (OSError, ValueError):
+        pass
     call_s = ms_per_step * 1e-3
     roofline_call = {
         "bound": "hbm", "algorithmic_GB": total_b / 1e9,

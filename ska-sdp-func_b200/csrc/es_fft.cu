@@ -302,6 +302,7 @@ __device__ __forceinline__ void fft_all_passes(T2* x, const EsFftLine& pl,
 struct EsFftLayout
 {
     int32_t lshift;    /* log2 of the columns per CTA of the column kernels */
+    int32_t rshift;    /* log2 of the rows per CTA of the row kernels */
     int32_t rows_pitch, cols_pitch;
     int64_t plane_elems; /* elements of T per plane (grid_size x image_size) */
     int32_t ntile, occ_nw; /* occupancy words: es_device.h */
@@ -343,9 +344,9 @@ __global__ void __launch_bounds__(ES_FFT_THREADS, 1) es_fft_grid_rows_kernel(
     extern __shared__ __align__(16) unsigned char es_fft_smem[];
     __shared__ uint32_t s_bits[ES_FFT_OCC_WORDS];
     T2* x = (T2*) es_fft_smem;
-    T2* tw = x + lay.rows_pitch;
+    T2* tw = x + ((size_t) lay.rows_pitch << lay.rshift);
     const int gsz = pl.n, n = image_size;
-    const int u = blockIdx.x;
+    const int u = blockIdx.x << lay.rshift; /* first row of the bundle */
     /* nothing was gridded onto this tile row: the column pass reads it as
      * zeros without it being stored */
     if (!occ_fetch(s_bits, occ_plane(occ, lay, blockIdx.y) +
@@ -354,22 +355,22 @@ __global__ void __launch_bounds__(ES_FFT_THREADS, 1) es_fft_grid_rows_kernel(
     in.bits = s_bits;
     in.base = planes + ((size_t) blockIdx.y * gsz + u) * gsz;
     in.estride = 1;
-    in.lstride = 0;
+    in.lstride = gsz;
     in.k0 = 0;
     in.count = gsz;
     in.any = 0u;
     LinearOut<T2, true> out;
     out.base = strip + (size_t) blockIdx.y * lay.plane_elems + (size_t) u * n;
     out.estride = 1;
-    out.lstride = 0;
+    out.lstride = n;
     out.k0 = gsz / 2 - n / 2;
     out.count = n;
     load_twiddles(tw, tw_g, pl.num_twiddles);
     __syncthreads();
     for (int step = 0; step < pl.num_stages; ++step)
     {
-        es_line_pass<1, false, T>(x, pl, step, tw, bpos, 0, lay.rows_pitch,
-                (int) threadIdx.x, (int) blockDim.x, in, out);
+        es_line_pass<1, false, T>(x, pl, step, tw, bpos, lay.rshift,
+                lay.rows_pitch, (int) threadIdx.x, (int) blockDim.x, in, out);
         if (step + 1 == pl.num_stages) break;
         if (step == 0)
         {
@@ -378,8 +379,9 @@ __global__ void __launch_bounds__(ES_FFT_THREADS, 1) es_fft_grid_rows_kernel(
             {
                 T2 zero;
                 zero.x = 0; zero.y = 0;
-                for (int i = threadIdx.x; i < n; i += blockDim.x)
-                    out.base[i] = zero;
+                for (int i = threadIdx.x; i < (n << lay.rshift);
+                        i += blockDim.x)
+                    out.base[i] = zero; /* the rows of a bundle are adjacent */
                 return;
             }
         }
@@ -507,16 +509,16 @@ __global__ void __launch_bounds__(ES_FFT_THREADS, 1) es_fft_degrid_rows_kernel(
     extern __shared__ __align__(16) unsigned char es_fft_smem[];
     __shared__ uint32_t s_bits[ES_FFT_OCC_WORDS];
     T2* x = (T2*) es_fft_smem;
-    T2* tw = x + lay.rows_pitch;
+    T2* tw = x + ((size_t) lay.rows_pitch << lay.rshift);
     const int gsz = pl.n, n = image_size;
-    const int u = blockIdx.x;
+    const int u = blockIdx.x << lay.rshift;
     /* only the tiles the gather reads are stored */
     if (!occ_fetch(s_bits, occ_plane(occ, lay, blockIdx.y) +
             (u >> 6) * lay.occ_nw, lay.occ_nw)) return;
     LinearIn<T2, true, false> in;
     in.base = strip + (size_t) blockIdx.y * lay.plane_elems + (size_t) u * n;
     in.estride = 1;
-    in.lstride = 0;
+    in.lstride = n;
     in.k0 = gsz / 2 - n / 2;
     in.count = n;
     in.any = 0u;
@@ -524,12 +526,13 @@ __global__ void __launch_bounds__(ES_FFT_THREADS, 1) es_fft_degrid_rows_kernel(
     out.bits = s_bits;
     out.base = planes + ((size_t) blockIdx.y * gsz + u) * gsz;
     out.estride = 1;
-    out.lstride = 0;
+    out.lstride = gsz;
     out.k0 = 0;
     out.count = gsz;
     load_twiddles(tw, tw_g, pl.num_twiddles);
     __syncthreads();
-    fft_all_passes<-1, true, T>(x, pl, tw, bpos, 0, lay.rows_pitch, in, out);
+    fft_all_passes<-1, true, T>(x, pl, tw, bpos, lay.rshift, lay.rows_pitch,
+            in, out);
 }
 
 /* ------------------------------------------------------ image transposes */
@@ -607,6 +610,7 @@ EsFftLayout fft_layout(const EsFft* f)
 {
     EsFftLayout lay;
     lay.lshift = f->cols.lshift;
+    lay.rshift = f->rows.lshift;
     lay.rows_pitch = f->rows.pitch;
     lay.cols_pitch = f->cols.pitch;
     lay.plane_elems = f->plane_elems;
@@ -665,15 +669,23 @@ int es_fft_create(int grid_size, int image_size, int is_double, EsFft** out)
     f->is_double = is_double;
     const size_t cplx = is_double ? 16 : 8;
     /* experiments: SKA_SDP_FUNC_ES_FFT_CFG="rows_threads,cols_threads,cols_lshift"
-     * default: bundles of 4 (fp64: 2) adjacent columns per CTA where they fit
+     * default: bundles of 4 (fp64: 2) adjacent columns / 2 (fp64: 1) rows per CTA where they fit
      * in shared memory (32-byte pieces of the row-major intermediate) */
-    int e[3] = {0, 0, is_double ? 1 : 2};
+    int e[4] = {0, 0, is_double ? 1 : 2, is_double ? 0 : 1};
     const char* env = getenv("SKA_SDP_FUNC_ES_FFT_CFG");
-    if (env) (void) sscanf(env, "%d,%d,%d", &e[0], &e[1], &e[2]);
+    if (env) (void) sscanf(env, "%d,%d,%d,%d", &e[0], &e[1], &e[2], &e[3]);
+    if (e[3] < 0 || e[3] > 2) e[3] = 0;
     for (int k = 0; k < 2; ++k)
         if (e[k] < 0 || e[k] > ES_FFT_THREADS || (e[k] & 31)) e[k] = 0;
     if (e[2] < 0 || e[2] > 2) e[2] = 0;
-    make_cfg(&f->line, cplx, 0, e[0], &f->rows);
+    /* rows of one CTA share a 64-row occupancy block and must tile the grid */
+    int rshift = e[3];
+    for (;; --rshift)
+    {
+        make_cfg(&f->line, cplx, rshift, e[0], &f->rows);
+        if ((f->rows.smem_bytes <= ES_FFT_MAX_SMEM &&
+                grid_size % (1 << rshift) == 0) || rshift == 0) break;
+    }
     int lshift = e[2];
     for (;; --lshift)
     {
@@ -769,7 +781,7 @@ int es_fft_grid_rows(const EsFft* f, const void* planes, int nplanes,
     cudaStream_t s = (cudaStream_t) stream;
     const EsFftLayout lay = fft_layout(f);
     const EsFftCfg& c = f->rows;
-    dim3 grid((unsigned) f->grid_size, (unsigned) nplanes);
+    dim3 grid((unsigned) (f->grid_size >> c.lshift), (unsigned) nplanes);
     if (f->is_double)
         es_fft_grid_rows_kernel<double><<<grid, c.threads, c.smem_bytes,
                 s>>>(f->line, (const double2*) f->d_tw, f->d_bpos,
@@ -831,7 +843,7 @@ int es_fft_degrid_rows(const EsFft* f, const void* strip, int nplanes,
     cudaStream_t s = (cudaStream_t) stream;
     const EsFftLayout lay = fft_layout(f);
     const EsFftCfg& c = f->rows;
-    dim3 grid((unsigned) f->grid_size, (unsigned) nplanes);
+    dim3 grid((unsigned) (f->grid_size >> c.lshift), (unsigned) nplanes);
     if (f->is_double)
         es_fft_degrid_rows_kernel<double><<<grid, c.threads, c.smem_bytes,
                 s>>>(f->line, (const double2*) f->d_tw, f->d_bpos,

@@ -42,6 +42,9 @@ struct sdp_GridderUvwEsFft
     EsGeom geom;
     double pixsize_x_rad, pixsize_y_rad;
     cudaStream_t stream;
+    cudaStream_t copy_stream; /* host staging of the array needed last */
+    cudaEvent_t copy_ev;
+    int32_t have_copy_stream;
 
     /* multi-GPU extension */
     int32_t plane_begin, plane_end, apply_correction;
@@ -327,6 +330,11 @@ void sdp_gridder_uvw_es_fft_free_plan(sdp_GridderUvwEsFft* plan)
     };
     for (size_t k = 0; k < sizeof(all) / sizeof(all[0]); ++k)
         buffer_free(all[k]);
+    if (plan->have_copy_stream)
+    {
+        (void) cudaEventDestroy(plan->copy_ev);
+        (void) cudaStreamDestroy(plan->copy_stream);
+    }
     if (plan->have_events)
         for (int k = 0; k < 8; ++k) (void) cudaEventDestroy(plan->ev[k]);
     for (int k = 0; k < plan->stage_cap; ++k)
@@ -679,13 +687,13 @@ static size_t mem_bytes(const sdp_Mem* m)
 }
 
 static void stage_in(sdp_GridderUvwEsFft* plan, EsBuffer* b,
-        const sdp_Mem* m, sdp_Error* status)
+        const sdp_Mem* m, cudaStream_t stream, sdp_Error* status)
 {
     const size_t bytes = mem_bytes(m);
     buffer_reserve(b, bytes > 0 ? bytes : 16, status);
     if (*status || bytes == 0) return;
     const cudaError_t err = cudaMemcpyAsync(b->ptr, sdp_mem_data_const(m),
-            bytes, cudaMemcpyHostToDevice, plan->stream);
+            bytes, cudaMemcpyHostToDevice, stream);
     if (err != cudaSuccess)
     {
         *status = SDP_ERR_MEM_COPY_FAILURE;
@@ -732,16 +740,44 @@ static void resolve_arrays(sdp_GridderUvwEsFft* plan, const sdp_Mem* uvw,
         return;
     }
     a->staged = 1;
-    stage_in(plan, &plan->st_uvw, uvw, status);
-    stage_in(plan, &plan->st_freq, freq_hz, status);
-    stage_in(plan, &plan->st_vis, vis, status);
-    if (need_weight) stage_in(plan, &plan->st_weight, weight, status);
-    stage_in(plan, &plan->st_dirty, dirty_image, status);
+    /* The array that is only needed at the end of the call (gridding: the
+     * image to accumulate into; degridding: the visibilities to add to) is
+     * copied on a second stream, overlapping the presort and the w-planes;
+     * the caller waits with late_copy_wait() before its first use. */
+    cudaStream_t late = plan->stream;
+    if (!plan->have_copy_stream &&
+            cudaStreamCreateWithFlags(&plan->copy_stream,
+                    cudaStreamNonBlocking) == cudaSuccess)
+    {
+        if (cudaEventCreateWithFlags(&plan->copy_ev,
+                cudaEventDisableTiming) == cudaSuccess)
+            plan->have_copy_stream = 1;
+        else
+            (void) cudaStreamDestroy(plan->copy_stream);
+    }
+    if (plan->have_copy_stream) late = plan->copy_stream;
+    stage_in(plan, &plan->st_uvw, uvw, plan->stream, status);
+    stage_in(plan, &plan->st_freq, freq_hz, plan->stream, status);
+    stage_in(plan, &plan->st_vis, vis, need_weight ? plan->stream : late,
+            status);
+    if (need_weight)
+        stage_in(plan, &plan->st_weight, weight, plan->stream, status);
+    stage_in(plan, &plan->st_dirty, dirty_image,
+            need_weight ? late : plan->stream, status);
+    if (plan->have_copy_stream)
+        (void) cudaEventRecord(plan->copy_ev, plan->copy_stream);
     a->uvw = plan->st_uvw.ptr;
     a->freq = plan->st_freq.ptr;
     a->vis = plan->st_vis.ptr;
     a->weight = plan->st_weight.ptr;
     a->dirty = plan->st_dirty.ptr;
+}
+
+/* Orders the main stream after the late staging copy of resolve_arrays. */
+static void late_copy_wait(sdp_GridderUvwEsFft* plan, const EsArrays* a)
+{
+    if (a->staged && plan->have_copy_stream)
+        (void) cudaStreamWaitEvent(plan->stream, plan->copy_ev, 0);
 }
 
 /* -------------------------------------------------------------- presort */
@@ -982,6 +1018,7 @@ void sdp_grid_uvw_es_fft(sdp_GridderUvwEsFft* plan, const sdp_Mem* uvw,
     presort(plan, &a, 1, &m, status);
     if (*status) return;
     plan->stats.num_entries = m;
+    if (!plan->pruned_fft) late_copy_wait(plan, &a); /* summed into per batch */
     if (plan->pruned_fft)
         ES_CUDA(cudaMemsetAsync(plan->image_t.ptr, 0, real_bytes(plan) *
                 (size_t) g->image_size * (size_t) g->image_size, s));
@@ -1038,6 +1075,7 @@ void sdp_grid_uvw_es_fft(sdp_GridderUvwEsFft* plan, const sdp_Mem* uvw,
     if (plan->pruned_fft)
     {
         /* dirty += transpose(accumulator) */
+        late_copy_wait(plan, &a);
         ES_CUDA(es_launch_transpose(plan->image_t.ptr, a.dirty,
                 g->image_size, g->is_double, 1, s));
         plan->stats.kernel_launches += 1;
@@ -1152,6 +1190,7 @@ void sdp_ifft_degrid_uvw_es(sdp_GridderUvwEsFft* plan, const sdp_Mem* uvw,
         plan->stats.planes_processed += nb;
     }
     event_mark(plan, 2);
+    late_copy_wait(plan, &a);
     ES_CUDA(es_launch_finish_degrid(g, plan->records.ptr, plan->acc.ptr, m,
             a.vis, s));
     plan->stats.kernel_launches += 1;
@@ -1185,7 +1224,7 @@ void sdp_gridder_uvw_es_fft_correct_image(sdp_GridderUvwEsFft* plan,
     const int staged = sdp_mem_location(dirty_image) != SDP_MEM_GPU;
     if (staged)
     {
-        stage_in(plan, &plan->st_dirty, dirty_image, status);
+        stage_in(plan, &plan->st_dirty, dirty_image, plan->stream, status);
         if (*status) return;
         d = plan->st_dirty.ptr;
     }
@@ -1227,8 +1266,8 @@ void sdp_gridder_uvw_es_fft_plane_histogram(sdp_GridderUvwEsFft* plan,
     const void* d_freq = sdp_mem_data_const(freq_hz);
     if (sdp_mem_location(uvw) != SDP_MEM_GPU)
     {
-        stage_in(plan, &plan->st_uvw, uvw, status);
-        stage_in(plan, &plan->st_freq, freq_hz, status);
+        stage_in(plan, &plan->st_uvw, uvw, plan->stream, status);
+        stage_in(plan, &plan->st_freq, freq_hz, plan->stream, status);
         if (*status) return;
         d_uvw = plan->st_uvw.ptr;
         d_freq = plan->st_freq.ptr;
