@@ -164,6 +164,7 @@ __global__ void __launch_bounds__(ES_SC_THREADS) es_scatter2_kernel(EsGeom g,
     T* s_kre = s_ku + CHUNK * NS;                      /* [CHUNK][NS] */
     T* s_kim = s_kre + CHUNK * NS;                     /* [CHUNK][NS] */
     int* s_pos = (int*) (s_kim + CHUNK * NS);          /* [CHUNK] */
+    uint32_t* s_band = (uint32_t*) (s_pos + CHUNK);    /* [CHUNK] bands a record touches */
     __shared__ uint32_t s_work;
     __shared__ int s_last;
 
@@ -227,6 +228,13 @@ __global__ void __launch_bounds__(ES_SC_THREADS) es_scatter2_kernel(EsGeom g,
                 const T vre = r.vre * kw, vim = r.vim * kw;
                 const int lu0 = r.lu0, lv0 = r.lv0;
                 s_pos[e] = (lu0 << 16) | (lv0 & 0xffff);
+                {
+                    /* bit w: the footprint rows overlap the band of warp w */
+                    const int b_lo = max(lu0, 0) / ES_SC_BAND;
+                    const int b_hi = min(lu0 + ns - 1, rows_valid - 1) / ES_SC_BAND;
+                    s_band[e] = (b_hi >= b_lo) ?
+                            ((2u << b_hi) - (1u << b_lo)) : 0u;
+                }
 #pragma unroll
                 for (int k = 0; k < NS; ++k)
                 {
@@ -244,13 +252,19 @@ __global__ void __launch_bounds__(ES_SC_THREADS) es_scatter2_kernel(EsGeom g,
             }
             __syncthreads();
             /* accumulate: this warp owns tile rows band_lo .. band_hi */
-            for (int e = 0; e < n; ++e)
+            for (int base = 0; base < n; base += 32)
             {
+            /* the records of this group of 32 that touch the warp's band */
+            unsigned todo = __ballot_sync(0xffffffffu, base + lane < n &&
+                    ((s_band[min(base + lane, n - 1)] >> warp) & 1u));
+            while (todo)
+            {
+                const int e = base + __ffs((int) todo) - 1;
+                todo &= todo - 1u;
                 const int pos = s_pos[e];
                 const int lu0 = pos >> 16;
                 const int r_lo = max(lu0, band_lo);
                 const int r_hi = min(lu0 + ns - 1, band_hi);
-                if (r_lo > r_hi) continue; /* warp-uniform */
                 const int col = (int) (short) (pos & 0xffff) + c;
                 if (lane_active && col >= 0 && col < cols_valid)
                 {
@@ -286,6 +300,7 @@ __global__ void __launch_bounds__(ES_SC_THREADS) es_scatter2_kernel(EsGeom g,
                         }
                     }
                 }
+            }
             }
         }
         __syncthreads();
@@ -339,7 +354,7 @@ size_t scatter2_smem()
 {
     typedef typename Prec<T>::T2 T2;
     return (size_t) ES_TILE * ES_TILE * sizeof(T2) +
-            (size_t) ScatterCfg<T>::CHUNK * (3 * NS * sizeof(T) + sizeof(int));
+            (size_t) ScatterCfg<T>::CHUNK * (3 * NS * sizeof(T) + 2 * sizeof(int));
 }
 
 template<typename T, int NS>
