@@ -149,7 +149,12 @@ template<typename T2, bool WINDOW, bool ANY, bool MASK = false> struct LinearIn
         c.step = (ptrdiff_t) gs * estride;
         return c;
     }
-    __device__ __forceinline__ T2 load(const Cursor& c, int k)
+    typedef T2 Raw;
+    __device__ __forceinline__ T2 finish(const Cursor&, int, const T2 v) const
+    {
+        return v;
+    }
+    __device__ __forceinline__ T2 fetch(const Cursor& c, int k)
     {
         T2 v;
         v.x = 0; v.y = 0;
@@ -257,13 +262,21 @@ template<typename T, typename T2> struct ScreenIn
         c.p = image_t + (ptrdiff_t) line * n + c.iu0;
         return c;
     }
-    __device__ __forceinline__ T2 load(const Cursor& c, int k) const
+    typedef T Raw;
+    /* the image value (0 outside the image); no arithmetic yet */
+    __device__ __forceinline__ T fetch(const Cursor& c, int k) const
+    {
+        const int iu = c.iu0 + k * c.gs;
+        T d = 0;
+        if ((unsigned) (iu + half) < (unsigned) n) d = c.p[k * c.gs];
+        return d;
+    }
+    __device__ __forceinline__ T2 finish(const Cursor& c, int k, T d) const
     {
         T2 o;
         o.x = 0; o.y = 0;
         const int iu = c.iu0 + k * c.gs;
         if ((unsigned) (iu + half) >= (unsigned) n) return o;
-        T d = c.p[k * c.gs];
         if ((iu + c.jv) & 1) d = -d;
         if (wstack)
         {

@@ -341,7 +341,8 @@ ES_HD int es_padded(const EsFftLine& pl, const int pos)
  *  - the first processed pass takes its inputs from `in` instead of x, the
  *    last one hands its outputs to `out`; both are addressed through a cursor
  *    c = cursor(line, index0, index_stride), element k of the butterfly being
- *    index0 + k * index_stride (load(c, k) / store(c, k, value)):
+ *    index0 + k * index_stride (raw = fetch(c, k), value = finish(c, k, raw) /
+ *    store(c, k, value)):
  *      natural-stride pass (stage 0):  index = j + k * stride0
  *      digit-reversed pass (last stage): index = t + k * (n / radix), where
  *      consecutive butterflies t own consecutive indices and bpos[t] is the
@@ -392,9 +393,15 @@ ES_HD void es_line_pass_body(T2* x, const EsFftLine& pl, const int stage,
         T2 v[R];
         if (from_in)
         {
+            /* two phases so that all R loads are in flight before the first
+             * value is used (the w-screen input functor does ~80 instructions
+             * of arithmetic per element) */
             const typename In::Cursor c = in.cursor(line, gidx, gstride);
+            typename In::Raw raw[R];
 #pragma unroll
-            for (int k = 0; k < R; ++k) v[k] = in.load(c, k);
+            for (int k = 0; k < R; ++k) raw[k] = in.fetch(c, k);
+#pragma unroll
+            for (int k = 0; k < R; ++k) v[k] = in.finish(c, k, raw[k]);
         }
         else
         {

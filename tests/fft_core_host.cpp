@@ -18,7 +18,9 @@ template<typename T> struct InF
     struct Cursor { const C2<T>* p; int gs; };
     const C2<T>* src; int n;
     Cursor cursor(int line, int idx0, int gs) const { return Cursor{src + (size_t) line * n + idx0, gs}; }
-    C2<T> load(const Cursor& c, int k) const { return c.p[k * c.gs]; }
+    typedef C2<T> Raw;
+    C2<T> fetch(const Cursor& c, int k) const { return c.p[k * c.gs]; }
+    C2<T> finish(const Cursor&, int, const C2<T> v) const { return v; }
 };
 template<typename T> struct OutF
 {
