@@ -17,10 +17,9 @@
  *                         accumulates its records into a 64x64 tile in shared
  *                         memory WITHOUT atomics: records are staged in chunks,
  *                         each thread evaluating the 2 (W+1) + 1 ES weights of
- *                         one record once; then each warp owns the tile
- *                         rows of every fourth 2-row stripe and walks the
- *                         chunk, its lanes covering (its rows x W+1 columns)
- *                         of a footprint. Unsplit units
+ *                         one record once; then each warp owns a band of 16
+ *                         tile rows and walks the chunk, its lanes covering
+ *                         (rows x W+1 columns) of a footprint. Unsplit units
  *                         flush the tile with coalesced 16-byte stores (this
  *                         is also the zero fill of the plane); split units
  *                         write partial tiles to scratch and the last slice to
@@ -141,7 +140,7 @@ __global__ void __launch_bounds__(256) es_occupancy_kernel(EsGeom g,
 /* ------------------------------------------------------------- scatter */
 
 #define ES_SC_THREADS 128
-static_assert(ES_SC_THREADS == 128, "the row stripes assume 4 warps");
+#define ES_SC_BAND (ES_TILE / (ES_SC_THREADS / 32))
 
 template<typename T> struct ScatterCfg;
 template<> struct ScatterCfg<float> { static const int CHUNK = 128; };
@@ -165,6 +164,7 @@ __global__ void __launch_bounds__(ES_SC_THREADS) es_scatter2_kernel(EsGeom g,
     T* s_kre = s_ku + CHUNK * NS;                      /* [CHUNK][NS] */
     T* s_kim = s_kre + CHUNK * NS;                     /* [CHUNK][NS] */
     int* s_pos = (int*) (s_kim + CHUNK * NS);          /* [CHUNK] */
+    uint32_t* s_band = (uint32_t*) (s_pos + CHUNK);    /* [CHUNK] bands a record touches */
     __shared__ uint32_t s_work;
     __shared__ int s_last;
 
@@ -211,6 +211,8 @@ __global__ void __launch_bounds__(ES_SC_THREADS) es_scatter2_kernel(EsGeom g,
             reinterpret_cast<float4*>(tile)[v] = make_float4(0.f, 0.f, 0.f, 0.f);
 
         const int plane = first_plane + u.plane_q;
+        const int band_lo = warp * ES_SC_BAND;
+        const int band_hi = min(band_lo + ES_SC_BAND, rows_valid) - 1;
         for (uint32_t chunk = u.a; chunk < u.b; chunk += CHUNK)
         {
             const int n = (int) min((uint32_t) CHUNK, u.b - chunk);
@@ -226,6 +228,13 @@ __global__ void __launch_bounds__(ES_SC_THREADS) es_scatter2_kernel(EsGeom g,
                 const T vre = r.vre * kw, vim = r.vim * kw;
                 const int lu0 = r.lu0, lv0 = r.lv0;
                 s_pos[e] = (lu0 << 16) | (lv0 & 0xffff);
+                {
+                    /* bit w: the footprint rows overlap the band of warp w */
+                    const int b_lo = max(lu0, 0) / ES_SC_BAND;
+                    const int b_hi = min(lu0 + ns - 1, rows_valid - 1) / ES_SC_BAND;
+                    s_band[e] = (b_hi >= b_lo) ?
+                            ((2u << b_hi) - (1u << b_lo)) : 0u;
+                }
 #pragma unroll
                 for (int k = 0; k < NS; ++k)
                 {
@@ -242,35 +251,56 @@ __global__ void __launch_bounds__(ES_SC_THREADS) es_scatter2_kernel(EsGeom g,
                 }
             }
             __syncthreads();
-            /* accumulate: warp w owns the tile rows r with ((r >> 1) & 3) == w
-             * (2-row stripes, interleaved), so every footprint gives every
-             * warp 2-3 rows: the warps stay balanced whatever the direction
-             * of the uv track, and a cell has one writer, in record order
-             * (bitwise reproducible, no atomics). Lane = (footprint column c,
-             * rsub-th owned row): W <= 8 takes one step per record. */
-            for (int e = 0; e < n; ++e)
+            /* accumulate: this warp owns tile rows band_lo .. band_hi */
+            for (int base = 0; base < n; base += 32)
             {
+            /* the records of this group of 32 that touch the warp's band */
+            unsigned todo = __ballot_sync(0xffffffffu, base + lane < n &&
+                    ((s_band[min(base + lane, n - 1)] >> warp) & 1u));
+            while (todo)
+            {
+                const int e = base + __ffs((int) todo) - 1;
+                todo &= todo - 1u;
                 const int pos = s_pos[e];
                 const int lu0 = pos >> 16;
+                const int r_lo = max(lu0, band_lo);
+                const int r_hi = min(lu0 + ns - 1, band_hi);
                 const int col = (int) (short) (pos & 0xffff) + c;
-                const int lo = max(lu0, 0);
-                const int hi = min(lu0 + ns - 1, rows_valid - 1);
-                const int base = (lo & ~7) + 2 * warp; /* first owned stripe */
-                const int skip = min(max(lo - base, 0), 2);
                 if (lane_active && col >= 0 && col < cols_valid)
                 {
                     const T pre = s_kre[e * NS + c], pim = s_kim[e * NS + c];
-                    for (int j = skip + rsub; ; j += rps)
+                    /* footprint rows of this lane, MS at a time: all loads,
+                     * then all updates, then all stores (distinct cells), so
+                     * the shared-memory round trip is paid once per record */
+                    constexpr int MS = (NS <= 9) ? 3 : 4;
+                    for (int rb = r_lo + rsub; rb <= r_hi; rb += MS * rps)
                     {
-                        const int r = base + ((j >> 1) << 3) + (j & 1);
-                        if (r > hi) break;
-                        const T ku = s_ku[e * NS + (r - lu0)];
-                        T2 cell = tile[r * ES_TILE + col];
-                        cell.x += pre * ku;
-                        cell.y += pim * ku;
-                        tile[r * ES_TILE + col] = cell;
+                        T2 cell[MS];
+                        T ku[MS];
+#pragma unroll
+                        for (int m = 0; m < MS; ++m)
+                        {
+                            const int r = rb + m * rps;
+                            if (r <= r_hi)
+                            {
+                                ku[m] = s_ku[e * NS + (r - lu0)];
+                                cell[m] = tile[r * ES_TILE + col];
+                            }
+                        }
+#pragma unroll
+                        for (int m = 0; m < MS; ++m)
+                        {
+                            const int r = rb + m * rps;
+                            if (r <= r_hi)
+                            {
+                                cell[m].x += pre * ku[m];
+                                cell[m].y += pim * ku[m];
+                                tile[r * ES_TILE + col] = cell[m];
+                            }
+                        }
                     }
                 }
+            }
             }
         }
         __syncthreads();
@@ -324,7 +354,7 @@ size_t scatter2_smem()
 {
     typedef typename Prec<T>::T2 T2;
     return (size_t) ES_TILE * ES_TILE * sizeof(T2) +
-            (size_t) ScatterCfg<T>::CHUNK * (3 * NS * sizeof(T) + sizeof(int));
+            (size_t) ScatterCfg<T>::CHUNK * (3 * NS * sizeof(T) + 2 * sizeof(int));
 }
 
 template<typename T, int NS>
