@@ -379,7 +379,20 @@ def run_product_arm(args):
     fence()
     elapsed_ms = start.elapsed_time(stop)
     stats = gridder.stats()          # stage times of the last timed step
+    extra = 0
+    if rank == 0 and world == 1:
+        # a short timed region can end before nvidia-smi's first sample (its
+        # start-up takes ~0.3 s): keep the same load running until there are
+        # two samples, so that the clocks line is always taken under load
+        deadline = time.time() + 6.0
+        while len(sampler.lines) < 2 and time.time() < deadline:
+            device_step()
+            torch.cuda.synchronize()
+            extra += 1
     clocks = sampler.stop() if rank == 0 else None
+    if clocks is not None and extra:
+        clocks["note"] = (f"{extra} extra untimed steps of the same load were run "
+                          "after the timed region until nvidia-smi had sampled")
     if world > 1:
         t = torch.tensor([elapsed_ms], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)

@@ -50,6 +50,7 @@
 struct EsFftCfg
 {
     int32_t threads, lshift, pitch;
+    int32_t tw_global; /* twiddle tables stay in global memory (L1): the line fills shared memory */
     size_t smem_bytes;
 };
 
@@ -70,10 +71,14 @@ template<typename T> struct Cx;
 template<> struct Cx<float> { typedef float2 T2; };
 template<> struct Cx<double> { typedef double2 T2; };
 
+/* Copies the tables to shared memory unless they are used in place. */
 template<typename T2>
-__device__ __forceinline__ void load_twiddles(T2* tw, const T2* tw_g, int count)
+__device__ __forceinline__ void load_twiddles(const T2* tw, const T2* tw_g,
+        int count)
 {
-    for (int i = threadIdx.x; i < count; i += blockDim.x) tw[i] = tw_g[i];
+    if (tw == tw_g) return;
+    T2* dst = const_cast<T2*>(tw);
+    for (int i = threadIdx.x; i < count; i += blockDim.x) dst[i] = tw_g[i];
 }
 
 /* ---- w-screen: exp(sign 2 pi i w (n - 1)) / n, n = sqrt(1 - l^2 - m^2),
@@ -319,6 +324,7 @@ struct EsFftLayout
     int32_t rows_pitch, cols_pitch;
     int64_t plane_elems; /* elements of T per plane (grid_size x image_size) */
     int32_t ntile, occ_nw; /* occupancy words: es_device.h */
+    int32_t rows_twg, cols_twg; /* twiddles read from global memory */
 };
 
 /* Words of plane q: tile bits of tile row tu at + tu * nw, the tile-row bits
@@ -357,7 +363,8 @@ __global__ void __launch_bounds__(ES_FFT_THREADS, 1) es_fft_grid_rows_kernel(
     extern __shared__ __align__(16) unsigned char es_fft_smem[];
     __shared__ uint32_t s_bits[ES_FFT_OCC_WORDS];
     T2* x = (T2*) es_fft_smem;
-    T2* tw = x + ((size_t) lay.rows_pitch << lay.rshift);
+    const T2* tw = lay.rows_twg ? tw_g :
+            x + ((size_t) lay.rows_pitch << lay.rshift);
     const int gsz = pl.n, n = image_size;
     const int u = blockIdx.x << lay.rshift; /* first row of the bundle */
     /* nothing was gridded onto this tile row: the column pass reads it as
@@ -425,7 +432,8 @@ es_fft_grid_cols_screen_kernel(const EsFftLine pl,
     extern __shared__ __align__(16) unsigned char es_fft_smem[];
     __shared__ uint32_t s_bits[ES_FFT_OCC_WORDS];
     T2* x = (T2*) es_fft_smem;
-    T2* tw = x + ((size_t) lay.cols_pitch << lay.lshift);
+    const T2* tw = lay.cols_twg ? tw_g :
+            x + ((size_t) lay.cols_pitch << lay.lshift);
     const int gsz = pl.n, n = g.image_size;
     const int col0 = blockIdx.x << lay.lshift;
     LinearIn<T2, false, false, true> in;
@@ -478,7 +486,8 @@ __global__ void __launch_bounds__(ES_FFT_THREADS, 1) es_fft_degrid_cols_kernel(
     extern __shared__ __align__(16) unsigned char es_fft_smem[];
     __shared__ uint32_t s_bits[ES_FFT_OCC_WORDS];
     T2* x = (T2*) es_fft_smem;
-    T2* tw = x + ((size_t) lay.cols_pitch << lay.lshift);
+    const T2* tw = lay.cols_twg ? tw_g :
+            x + ((size_t) lay.cols_pitch << lay.lshift);
     const int gsz = pl.n, n = g.image_size;
     const int q = blockIdx.x % nplanes;
     const int col0 = (blockIdx.x / nplanes) << lay.lshift;
@@ -522,7 +531,8 @@ __global__ void __launch_bounds__(ES_FFT_THREADS, 1) es_fft_degrid_rows_kernel(
     extern __shared__ __align__(16) unsigned char es_fft_smem[];
     __shared__ uint32_t s_bits[ES_FFT_OCC_WORDS];
     T2* x = (T2*) es_fft_smem;
-    T2* tw = x + ((size_t) lay.rows_pitch << lay.rshift);
+    const T2* tw = lay.rows_twg ? tw_g :
+            x + ((size_t) lay.rows_pitch << lay.rshift);
     const int gsz = pl.n, n = image_size;
     const int u = blockIdx.x << lay.rshift;
     /* only the tiles the gather reads are stored */
@@ -597,8 +607,19 @@ void make_cfg(const EsFftLine* line, size_t cplx, int lshift, int threads,
 {
     c->lshift = lshift;
     c->pitch = bundle_pitch(line, lshift);
+    c->tw_global = 0;
     c->smem_bytes = ((size_t) c->pitch << lshift) * cplx +
             (size_t) (line->num_twiddles + 1) * cplx;
+    /* tests: SKA_SDP_FUNC_ES_FFT_TW_GLOBAL=1 forces this mode at any size */
+    const bool force = getenv("SKA_SDP_FUNC_ES_FFT_TW_GLOBAL") != 0;
+    if (force || (c->smem_bytes > ES_FFT_MAX_SMEM && lshift == 0 &&
+            (size_t) c->pitch * cplx <= ES_FFT_MAX_SMEM))
+    {
+        /* e.g. fp64 lines of 14400 elements (230 KB): everything but the
+         * line itself leaves shared memory */
+        c->tw_global = 1;
+        c->smem_bytes = ((size_t) c->pitch << lshift) * cplx;
+    }
     if (threads <= 0)
     {
         /* as many CTAs per SM as shared memory allows (at most 4), all of
@@ -624,6 +645,8 @@ EsFftLayout fft_layout(const EsFft* f)
     EsFftLayout lay;
     lay.lshift = f->cols.lshift;
     lay.rshift = f->rows.lshift;
+    lay.rows_twg = f->rows.tw_global;
+    lay.cols_twg = f->cols.tw_global;
     lay.rows_pitch = f->rows.pitch;
     lay.cols_pitch = f->cols.pitch;
     lay.plane_elems = f->plane_elems;

@@ -264,3 +264,13 @@ def test_sparse_coverage_after_dense_call_on_the_same_plan(single):
     v2, _, _ = product_degrid(sparse, eps, True, g)
     assert rel_max(d2, oracle_grid(sparse, eps, True)) <= tol
     assert rel_max(v2, oracle_degrid(sparse, eps, True)[0]) <= tol
+
+
+@pytest.mark.parametrize("single", [True, False])
+def test_twiddles_in_global_memory_mode(monkeypatch, single):
+    """Lines that fill shared memory (fp64, G = 14400: BASELINE config C3) keep
+    the twiddle tables in global memory (es_fft.cu: tw_global). The mode is
+    forced here on a small case so that it is checked against the oracle."""
+    monkeypatch.setenv("SKA_SDP_FUNC_ES_FFT_TW_GLOBAL", "1")
+    c = synth.reference_test_case(256, num_vis=300, num_chan=6, single=single)
+    check_parity(c, 1e-5 if single else 1e-9, True)
