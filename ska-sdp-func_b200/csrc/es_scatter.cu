@@ -15,11 +15,15 @@
  *                         planes); without the split one CTA does all of it.
  *   es_scatter2_kernel    persistent CTAs pull units from the list. A unit
  *                         accumulates its records into a 64x64 tile in shared
- *                         memory WITHOUT atomics: records are staged in chunks,
- *                         each thread evaluating the 2 (W+1) + 1 ES weights of
- *                         one record once; then each warp owns a band of 16
- *                         tile rows and walks the chunk, its lanes covering
- *                         (rows x W+1 columns) of a footprint. Unsplit units
+ *                         memory WITHOUT atomics: each warp owns a band of 16
+ *                         tile rows. fp32: every warp walks the unit's records
+ *                         on its own (no CTA barrier inside a unit), stages
+ *                         the 2 (W+1) + 1 ES weights of the records touching
+ *                         its band (one record per lane) and accumulates them,
+ *                         its lanes covering (rows x W+1 columns) of a
+ *                         footprint. fp64: the weights are staged once per
+ *                         record CTA-wide, then each warp visits the records
+ *                         of its band (ballot-compacted). Unsplit units
  *                         flush the tile with coalesced 16-byte stores (this
  *                         is also the zero fill of the plane); split units
  *                         write partial tiles to scratch and the last slice to
@@ -164,7 +168,7 @@ __global__ void __launch_bounds__(ES_SC_THREADS) es_scatter2_kernel(EsGeom g,
     T* s_kre = s_ku + CHUNK * NS;                      /* [CHUNK][NS] */
     T* s_kim = s_kre + CHUNK * NS;                     /* [CHUNK][NS] */
     int* s_pos = (int*) (s_kim + CHUNK * NS);          /* [CHUNK] */
-    uint32_t* s_band = (uint32_t*) (s_pos + CHUNK);    /* [CHUNK] bands a record touches */
+    uint32_t* s_band = (uint32_t*) (s_pos + CHUNK);    /* [CHUNK] bands a record touches (fp64 path) */
     __shared__ uint32_t s_work;
     __shared__ int s_last;
 
@@ -213,6 +217,109 @@ __global__ void __launch_bounds__(ES_SC_THREADS) es_scatter2_kernel(EsGeom g,
         const int plane = first_plane + u.plane_q;
         const int band_lo = warp * ES_SC_BAND;
         const int band_hi = min(band_lo + ES_SC_BAND, rows_valid) - 1;
+        __syncthreads(); /* tile zeroed */
+        /* Each warp walks the unit's records on its own (no CTA barrier
+         * inside a unit): it picks the records whose footprint rows touch
+         * its band, stages their ES weights into its private slice of the
+         * staging arrays (one record per lane, kernels.cu:201-221 with the
+         * signs of :233-235 folded in) and accumulates them in record order.
+         * A record touching two bands is staged by both warps. */
+        if constexpr (sizeof(T) == 4)
+        {
+            constexpr int WCH = CHUNK / (ES_SC_THREADS / 32); /* per warp */
+            T* w_ku = s_ku + warp * WCH * NS;
+            T* w_kre = s_kre + warp * WCH * NS;
+            T* w_kim = s_kim + warp * WCH * NS;
+            int* w_pos = s_pos + warp * WCH;
+            for (uint32_t base = u.a; base < u.b; base += WCH)
+            {
+                const uint32_t idx = base + (uint32_t) lane;
+                bool mine = false;
+                Rec r;
+                if (lane < WCH && idx < u.b)
+                {
+                    r = records[idx];
+                    mine = max((int) r.lu0, band_lo) <=
+                            min((int) r.lu0 + ns - 1, band_hi);
+                }
+                const unsigned m = __ballot_sync(0xffffffffu, mine);
+                if (m == 0u) continue; /* warp-uniform */
+                __syncwarp(); /* the previous group's weights are consumed */
+                if (mine)
+                {
+                    const int e = __popc(m & ((1u << lane) - 1u));
+                    const int dp = plane - r.p0;
+                    const T kw = (dp >= 0 && dp <= g.support) ?
+                            es_psi(beta, ((T) dp + r.dw) * inv_hs) : (T) 0;
+                    const T vre = r.vre * kw, vim = r.vim * kw;
+                    const int lu0 = r.lu0, lv0 = r.lv0;
+                    w_pos[e] = (lu0 << 16) | (lv0 & 0xffff);
+#pragma unroll
+                    for (int k = 0; k < NS; ++k)
+                    {
+                        if (k < ns)
+                        {
+                            T ku = es_psi(beta, ((T) k + r.du) * inv_hs);
+                            T kv = es_psi(beta, ((T) k + r.dv) * inv_hs);
+                            if ((lu0 + k) & 1) ku = -ku;
+                            if ((lv0 + k) & 1) kv = -kv;
+                            w_ku[e * NS + k] = ku;
+                            w_kre[e * NS + k] = vre * kv;
+                            w_kim[e * NS + k] = vim * kv;
+                        }
+                    }
+                }
+                __syncwarp();
+                const int cnt = __popc(m);
+                for (int e = 0; e < cnt; ++e)
+                {
+                    const int pos = w_pos[e];
+                    const int lu0 = pos >> 16;
+                    const int r_lo = max(lu0, band_lo);
+                    const int r_hi = min(lu0 + ns - 1, band_hi);
+                    const int col = (int) (short) (pos & 0xffff) + c;
+                    if (lane_active && col >= 0 && col < cols_valid)
+                    {
+                        const T pre = w_kre[e * NS + c], pim = w_kim[e * NS + c];
+                        /* footprint rows of this lane, MS at a time: all
+                         * loads, then all updates, then all stores (distinct
+                         * cells): one shared-memory round trip per record */
+                        constexpr int MS = (NS <= 9) ? 3 : 4;
+                        for (int rb = r_lo + rsub; rb <= r_hi; rb += MS * rps)
+                        {
+                            T2 cell[MS];
+                            T ku[MS];
+#pragma unroll
+                            for (int mm = 0; mm < MS; ++mm)
+                            {
+                                const int rr = rb + mm * rps;
+                                if (rr <= r_hi)
+                                {
+                                    ku[mm] = w_ku[e * NS + (rr - lu0)];
+                                    cell[mm] = tile[rr * ES_TILE + col];
+                                }
+                            }
+#pragma unroll
+                            for (int mm = 0; mm < MS; ++mm)
+                            {
+                                const int rr = rb + mm * rps;
+                                if (rr <= r_hi)
+                                {
+                                    cell[mm].x += pre * ku[mm];
+                                    cell[mm].y += pim * ku[mm];
+                                    tile[rr * ES_TILE + col] = cell[mm];
+                                }
+                            }
+                        }
+                    }
+                }
+            }
+        }
+        else
+        {
+        /* fp64: the ES weights are too expensive to evaluate twice for
+         * records touching two bands: CTA-wide staging, one record per
+         * thread, then the band walk */
         for (uint32_t chunk = u.a; chunk < u.b; chunk += CHUNK)
         {
             const int n = (int) min((uint32_t) CHUNK, u.b - chunk);
@@ -302,6 +409,7 @@ __global__ void __launch_bounds__(ES_SC_THREADS) es_scatter2_kernel(EsGeom g,
                 }
             }
             }
+        }
         }
         __syncthreads();
         if (u.num_slices == 1)
