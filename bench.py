@@ -544,6 +544,9 @@ def run_product_arm(args):
         if tr:
             roofline["traffic"] = tr["dram_bytes_per_launch"]
             roofline["traffic_source"] = tr["source"]
+            # same capture: share of cycles with an instruction issued (the
+            # limiter ncu reports for the line-FFT kernels)
+            roofline["ncu_issue_active_pct"] = tr.get("issue_active_pct")
     except (OSError, ValueError):
         pass
     call_s = ms_per_step * 1e-3
