@@ -44,7 +44,7 @@
 #include "es_screen.h"
 
 #define ES_FFT_THREADS 512 /* upper bound of the CTA size (128 registers each) */
-#define ES_FFT_MAX_SMEM (227 * 1024 - 64) /* 64 B of static occupancy words */
+#define ES_FFT_MAX_SMEM (227 * 1024 - 512) /* 512 B of static occupancy flags */
 
 /* CTA shape of one kernel family. */
 struct EsFftCfg
@@ -122,14 +122,16 @@ template<> struct Screen<double>
  * [k0, k0 + count) read as zero / are not stored (the pruning). */
 
 /* MASK: index idx (k0 == 0) belongs to 64-wide block idx >> 6; blocks whose
- * bit in `bits` (shared memory) is clear read as zero / are not stored. */
+ * flag in `bits` (shared memory, one byte per block: occ_fetch expands the
+ * occupancy words, so the test is a shift, a byte load and a compare) is
+ * clear read as zero / are not stored. */
 #define ES_FFT_OCC_WORDS 16 /* blocks <= 512: lines up to 32768 elements */
+#define ES_FFT_OCC_BYTES (ES_FFT_OCC_WORDS * 32)
 static_assert(ES_TILE == 64, "occupancy blocks are addressed with idx >> 6");
 
-__device__ __forceinline__ bool occ_bit(const uint32_t* bits, int idx)
+__device__ __forceinline__ bool occ_bit(const uint8_t* bits, int idx)
 {
-    const int t = idx >> 6;
-    return (bits[t >> 5] >> (t & 31)) & 1u;
+    return bits[idx >> 6] != 0;
 }
 
 template<typename T2, bool WINDOW, bool ANY, bool MASK = false> struct LinearIn
@@ -143,7 +145,7 @@ template<typename T2, bool WINDOW, bool ANY, bool MASK = false> struct LinearIn
     const T2* base;          /* element k0 of line 0 */
     ptrdiff_t estride, lstride;
     int k0, count;
-    const uint32_t* bits;    /* MASK */
+    const uint8_t* bits;     /* MASK */
     unsigned int any;        /* ANY: becomes non-zero when a loaded value is */
     __device__ __forceinline__ Cursor cursor(int line, int idx0, int gs) const
     {
@@ -182,7 +184,7 @@ template<typename T2, bool WINDOW, bool MASK = false> struct LinearOut
     T2* base;
     ptrdiff_t estride, lstride;
     int k0, count;
-    const uint32_t* bits;    /* MASK */
+    const uint8_t* bits;     /* MASK */
     __device__ __forceinline__ Cursor cursor(int line, int idx0, int gs) const
     {
         Cursor c;
@@ -335,18 +337,20 @@ __device__ __forceinline__ const uint32_t* occ_plane(const uint32_t* occ,
     return occ + (size_t) q * (size_t) ((lay.ntile + 1) * lay.occ_nw);
 }
 
-/* Copies nw words to shared memory; true when any of them is non-zero
- * (contains a barrier: every thread of the CTA must call it). */
-__device__ __forceinline__ bool occ_fetch(uint32_t* s_bits,
+/* Expands the nw occupancy words at src into one byte per block in shared
+ * memory; true when any block is occupied (contains a barrier: every thread
+ * of the CTA must call it). */
+__device__ __forceinline__ bool occ_fetch(uint8_t* s_bits,
         const uint32_t* src, int nw)
 {
-    uint32_t w = 0;
-    if ((int) threadIdx.x < nw)
+    uint32_t any = 0;
+    for (int t = threadIdx.x; t < nw * 32; t += blockDim.x)
     {
-        w = src[threadIdx.x];
-        s_bits[threadIdx.x] = w;
+        const uint32_t b = (src[t >> 5] >> (t & 31)) & 1u;
+        s_bits[t] = (uint8_t) b;
+        any |= b;
     }
-    return __syncthreads_or((int) (w != 0u)) != 0;
+    return __syncthreads_or((int) any) != 0;
 }
 
 /* ------------------------------------------------------ gridding pass 1 */
@@ -361,7 +365,7 @@ __global__ void __launch_bounds__(ES_FFT_THREADS, 1) es_fft_grid_rows_kernel(
 {
     typedef typename Cx<T>::T2 T2;
     extern __shared__ __align__(16) unsigned char es_fft_smem[];
-    __shared__ uint32_t s_bits[ES_FFT_OCC_WORDS];
+    __shared__ uint8_t s_bits[ES_FFT_OCC_BYTES];
     T2* x = (T2*) es_fft_smem;
     const T2* tw = lay.rows_twg ? tw_g :
             x + ((size_t) lay.rows_pitch << lay.rshift);
@@ -430,7 +434,7 @@ es_fft_grid_cols_screen_kernel(const EsFftLine pl,
 {
     typedef typename Cx<T>::T2 T2;
     extern __shared__ __align__(16) unsigned char es_fft_smem[];
-    __shared__ uint32_t s_bits[ES_FFT_OCC_WORDS];
+    __shared__ uint8_t s_bits[ES_FFT_OCC_BYTES];
     T2* x = (T2*) es_fft_smem;
     const T2* tw = lay.cols_twg ? tw_g :
             x + ((size_t) lay.cols_pitch << lay.lshift);
@@ -484,7 +488,7 @@ __global__ void __launch_bounds__(ES_FFT_THREADS, 1) es_fft_degrid_cols_kernel(
 {
     typedef typename Cx<T>::T2 T2;
     extern __shared__ __align__(16) unsigned char es_fft_smem[];
-    __shared__ uint32_t s_bits[ES_FFT_OCC_WORDS];
+    __shared__ uint8_t s_bits[ES_FFT_OCC_BYTES];
     T2* x = (T2*) es_fft_smem;
     const T2* tw = lay.cols_twg ? tw_g :
             x + ((size_t) lay.cols_pitch << lay.lshift);
@@ -529,7 +533,7 @@ __global__ void __launch_bounds__(ES_FFT_THREADS, 1) es_fft_degrid_rows_kernel(
 {
     typedef typename Cx<T>::T2 T2;
     extern __shared__ __align__(16) unsigned char es_fft_smem[];
-    __shared__ uint32_t s_bits[ES_FFT_OCC_WORDS];
+    __shared__ uint8_t s_bits[ES_FFT_OCC_BYTES];
     T2* x = (T2*) es_fft_smem;
     const T2* tw = lay.rows_twg ? tw_g :
             x + ((size_t) lay.rows_pitch << lay.rshift);
