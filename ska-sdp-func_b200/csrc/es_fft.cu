@@ -161,6 +161,12 @@ template<typename T2, bool WINDOW, bool ANY, bool MASK = false> struct LinearIn
     {
         return v;
     }
+    __device__ __forceinline__ void finish2(const Cursor&, int, const T2 r0,
+            const T2 r1, T2& v0, T2& v1) const
+    {
+        v0 = r0;
+        v1 = r1;
+    }
     __device__ __forceinline__ T2 fetch(const Cursor& c, int k)
     {
         T2 v;
@@ -199,6 +205,12 @@ template<typename T2, bool WINDOW, bool MASK = false> struct LinearOut
         if ((!WINDOW || (unsigned) (c.r0 + k * c.gs) < (unsigned) count) &&
                 (!MASK || occ_bit(bits, c.r0 + k * c.gs)))
             c.p[k * c.step] = v;
+    }
+    __device__ __forceinline__ void store2(const Cursor& c, int k, const T2 v0,
+            const T2 v1) const
+    {
+        store(c, k, v0);
+        store(c, k + 1, v1);
     }
 };
 
@@ -242,6 +254,32 @@ template<typename T, typename T2> struct ScreenOut
         }
         if ((iu + c.jv) & 1) val = -val;
         atomicAdd(c.p + k * c.gs, val);
+    }
+    /* outputs k and k + 1: when both fall into the image (the common case)
+     * the two phasors are evaluated side by side without a branch between */
+    __device__ __forceinline__ void store2(const Cursor& c, int k, const T2 v0,
+            const T2 v1) const
+    {
+        const int iu0 = c.iu0 + k * c.gs, iu1 = iu0 + c.gs;
+        const bool in0 = (unsigned) (iu0 + half) < (unsigned) n;
+        const bool in1 = (unsigned) (iu1 + half) < (unsigned) n;
+        if (!(in0 && in1) || !wstack)
+        {
+            if (in0) store(c, k, v0);
+            if (in1) store(c, k + 1, v1);
+            return;
+        }
+        T cr0, ci0, inv0, cr1, ci1, inv1;
+        Screen<T>::eval((uint32_t) (iu0 * iu0) + c.jv2, pix2, pix2f, -w,
+                cr0, ci0, inv0);
+        Screen<T>::eval((uint32_t) (iu1 * iu1) + c.jv2, pix2, pix2f, -w,
+                cr1, ci1, inv1);
+        T val0 = (v0.x * cr0 - v0.y * ci0) * inv0;
+        T val1 = (v1.x * cr1 - v1.y * ci1) * inv1;
+        if ((iu0 + c.jv) & 1) val0 = -val0;
+        if ((iu1 + c.jv) & 1) val1 = -val1;
+        atomicAdd(c.p + k * c.gs, val0);
+        atomicAdd(c.p + (k + 1) * c.gs, val1);
     }
 };
 
@@ -299,6 +337,32 @@ template<typename T, typename T2> struct ScreenIn
             o.x = d;
         }
         return o;
+    }
+    /* elements k and k + 1: both inside the image (the common case) -> the
+     * two phasors are evaluated side by side without a branch between */
+    __device__ __forceinline__ void finish2(const Cursor& c, int k, T d0, T d1,
+            T2& o0, T2& o1) const
+    {
+        const int iu0 = c.iu0 + k * c.gs, iu1 = iu0 + c.gs;
+        const bool in0 = (unsigned) (iu0 + half) < (unsigned) n;
+        const bool in1 = (unsigned) (iu1 + half) < (unsigned) n;
+        if (!(in0 && in1) || !wstack)
+        {
+            o0 = finish(c, k, d0);
+            o1 = finish(c, k + 1, d1);
+            return;
+        }
+        T cr0, ci0, inv0, cr1, ci1, inv1;
+        Screen<T>::eval((uint32_t) (iu0 * iu0) + c.jv2, pix2, pix2f, w,
+                cr0, ci0, inv0);
+        Screen<T>::eval((uint32_t) (iu1 * iu1) + c.jv2, pix2, pix2f, w,
+                cr1, ci1, inv1);
+        if ((iu0 + c.jv) & 1) d0 = -d0;
+        if ((iu1 + c.jv) & 1) d1 = -d1;
+        d0 *= inv0;
+        d1 *= inv1;
+        o0.x = cr0 * d0; o0.y = ci0 * d0;
+        o1.x = cr1 * d1; o1.y = ci1 * d1;
     }
 };
 

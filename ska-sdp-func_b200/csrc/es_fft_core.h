@@ -401,7 +401,9 @@ ES_HD void es_line_pass_body(T2* x, const EsFftLine& pl, const int stage,
 #pragma unroll
             for (int k = 0; k < R; ++k) raw[k] = in.fetch(c, k);
 #pragma unroll
-            for (int k = 0; k < R; ++k) v[k] = in.finish(c, k, raw[k]);
+            for (int k = 0; k + 1 < R; k += 2)
+                in.finish2(c, k, raw[k], raw[k + 1], v[k], v[k + 1]);
+            if (R & 1) v[R - 1] = in.finish(c, R - 1, raw[R - 1]);
         }
         else
         {
@@ -412,9 +414,14 @@ ES_HD void es_line_pass_body(T2* x, const EsFftLine& pl, const int stage,
         if (to_out)
         {
             const typename Out::Cursor c = out.cursor(line, gidx, gstride);
+            /* two outputs per call: the w-screen output functor evaluates
+             * both phasors in one straight-line block (instruction-level
+             * parallelism for its long dependent chains) */
 #pragma unroll
-            for (int k = 0; k < R; ++k)
-                out.store(c, k, v[es_out_slot<R>(k)]);
+            for (int k = 0; k + 1 < R; k += 2)
+                out.store2(c, k, v[es_out_slot<R>(k)],
+                        v[es_out_slot<R>(k + 1)]);
+            if (R & 1) out.store(c, R - 1, v[es_out_slot<R>(R - 1)]);
         }
         else
         {
