@@ -931,18 +931,23 @@ int es_launch_gather2(const EsGeom* g, const void* records, const void* units,
         void* acc, es_stream_t stream)
 {
     cudaStream_t s = (cudaStream_t) stream;
-    const bool wide = g->support + 1 > 9;
+    /* footprint slots per axis the kernel is unrolled for: 9, 13 or 17 */
+    const int ns = g->support + 1;
     if (g->is_double)
-        return wide ?
-            launch_gather2_ts<double, 17>(g, records, units, counters,
-                    first_plane, nplanes, planes, acc, s) :
-            launch_gather2_ts<double, 9>(g, records, units, counters,
-                    first_plane, nplanes, planes, acc, s);
-    return wide ?
-        launch_gather2_ts<float, 17>(g, records, units, counters, first_plane,
-                nplanes, planes, acc, s) :
-        launch_gather2_ts<float, 9>(g, records, units, counters, first_plane,
-                nplanes, planes, acc, s);
+    {
+        if (ns <= 9) return launch_gather2_ts<double, 9>(g, records, units,
+                counters, first_plane, nplanes, planes, acc, s);
+        if (ns <= 13) return launch_gather2_ts<double, 13>(g, records, units,
+                counters, first_plane, nplanes, planes, acc, s);
+        return launch_gather2_ts<double, 17>(g, records, units, counters,
+                first_plane, nplanes, planes, acc, s);
+    }
+    if (ns <= 9) return launch_gather2_ts<float, 9>(g, records, units,
+            counters, first_plane, nplanes, planes, acc, s);
+    if (ns <= 13) return launch_gather2_ts<float, 13>(g, records, units,
+            counters, first_plane, nplanes, planes, acc, s);
+    return launch_gather2_ts<float, 17>(g, records, units, counters,
+            first_plane, nplanes, planes, acc, s);
 }
 
 int es_launch_finish_degrid(const EsGeom* g, const void* records,

@@ -552,18 +552,23 @@ int es_launch_scatter2(const EsGeom* g, const void* records, const void* units,
         uint32_t* split_done, es_stream_t stream)
 {
     cudaStream_t s = (cudaStream_t) stream;
-    const bool wide = g->support + 1 > 9;
+    /* footprint slots per axis the kernel is unrolled for: 9, 13 or 17 */
+    const int ns = g->support + 1;
     if (g->is_double)
-        return wide ?
-            launch_scatter2_t<double, 17>(g, records, units, counters,
-                    first_plane, planes, scratch, split_done, s) :
-            launch_scatter2_t<double, 9>(g, records, units, counters,
-                    first_plane, planes, scratch, split_done, s);
-    return wide ?
-        launch_scatter2_t<float, 17>(g, records, units, counters, first_plane,
-                planes, scratch, split_done, s) :
-        launch_scatter2_t<float, 9>(g, records, units, counters, first_plane,
-                planes, scratch, split_done, s);
+    {
+        if (ns <= 9) return launch_scatter2_t<double, 9>(g, records, units,
+                counters, first_plane, planes, scratch, split_done, s);
+        if (ns <= 13) return launch_scatter2_t<double, 13>(g, records, units,
+                counters, first_plane, planes, scratch, split_done, s);
+        return launch_scatter2_t<double, 17>(g, records, units, counters,
+                first_plane, planes, scratch, split_done, s);
+    }
+    if (ns <= 9) return launch_scatter2_t<float, 9>(g, records, units,
+            counters, first_plane, planes, scratch, split_done, s);
+    if (ns <= 13) return launch_scatter2_t<float, 13>(g, records, units,
+            counters, first_plane, planes, scratch, split_done, s);
+    return launch_scatter2_t<float, 17>(g, records, units, counters,
+            first_plane, planes, scratch, split_done, s);
 }
 
 } // extern "C"
