@@ -148,7 +148,7 @@ __global__ void __launch_bounds__(256) es_occupancy_kernel(EsGeom g,
 
 template<typename T> struct ScatterCfg;
 template<> struct ScatterCfg<float> { static const int CHUNK = 128; };
-template<> struct ScatterCfg<double> { static const int CHUNK = 64; };
+template<> struct ScatterCfg<double> { static const int CHUNK = 32; };
 
 /* NS: footprint slots per axis the staging arrays hold (support + 1 <= NS). */
 template<typename T, int NS>
