@@ -27,7 +27,7 @@
 #include "es_plan.h"
 #include "ska-sdp-func/grid_data/sdp_gridder_uvw_es_fft_b200.h"
 
-#define ES_MAX_PLANE_BATCH 8
+#define ES_MAX_PLANE_BATCH 24
 #define ES_NUM_FFT_PLANS 2
 
 typedef struct EsBuffer
@@ -389,7 +389,8 @@ static int choose_plane_batch(const sdp_GridderUvwEsFft* plan)
     const double per_plane = plan->pruned_fft ?
             plane_bytes * (1.0 + (double) plan->info.image_size /
                     (double) plan->info.grid_size) : 2.0 * plane_bytes;
-    int fit = (int) (0.35 * (double) free_b / per_plane);
+    /* the presort scratch, records and staging copies need room too */
+    int fit = (int) (0.55 * (double) free_b / per_plane);
     if (fit < 1) fit = 1;
     int batch = plan->info.num_total_w_grids;
     if (batch > limit) batch = limit;
