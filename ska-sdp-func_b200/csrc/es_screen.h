@@ -8,10 +8,9 @@
  *
  * The phase w (n - 1) reaches 1e2 .. 1e4 turns, so n - 1 needs ~1e-13: it is
  * formed in fp64 in both precisions. For fp32 data everything that would go
- * through the 16-lane conversion / special-function unit (int <-> fp64,
- * fp32 <-> fp64, rint, sincospi's float -> int) is done with integer and
- * FMA-pipe instructions instead; the only special-function instruction left
- * is one MUFU.RSQ seed per pixel:
+ * through the 16-lane conversion / special-function unit (rint, sincospi's
+ * float -> int) is done with integer and FMA-pipe instructions instead; the
+ * int / fp32 <-> fp64 conversions exist in both forms (see es_screen_f32):
  *   1/n   = fp32 rsqrt seed + one Newton step in fp64       (rel. err ~2e-14)
  *   n - 1 = (1 - l^2 - m^2) / n - 1
  *   t     = w (n - 1) - round(w (n - 1))  (magic-constant rounding, fp64)
@@ -138,6 +137,25 @@ ES_SCR_HD void es_screen_f32(const uint32_t s, const double pix2,
         const float pix2f, const double w_signed, float& re, float& im,
         float& inv_n)
 {
+#if !defined(ES_SCREEN_INTEGER_CVT) && defined(__CUDA_ARCH__)
+    /* device default: hardware conversions (quarter-rate unit, but one issue
+     * slot each; with two phasors evaluated side by side they measured 2-3 %
+     * faster in the column kernels than the integer forms below, which the
+     * host build and -DES_SCREEN_INTEGER_CVT keep) */
+    const double a = 1.0 - pix2 * (double) s;
+    const float af = 1.0f - pix2f * (float) s;
+    const float y0 = rsqrtf(af);
+    const double yd = (double) y0;
+    const double h = a * yd;
+    const double e = 1.0 - h * yd;
+    const double y = yd + (0.5 * yd) * e;
+    const double nm1 = a * y - 1.0;
+    double t = w_signed * nm1;
+    const double big = 6755399441055744.0;
+    t -= (t + big) - big;
+    es_sincos_turns(__double2float_rz(t), re, im);
+    inv_n = __double2float_rz(y);
+#else
     const double a = 1.0 - pix2 * es_uint_to_double(s);
     const float af = 1.0f - pix2f * (float) s;
 #if defined(__CUDA_ARCH__)
@@ -155,6 +173,7 @@ ES_SCR_HD void es_screen_f32(const uint32_t s, const double pix2,
     t -= (t + big) - big;
     es_sincos_turns(es_double_to_float(t), re, im);
     inv_n = es_double_to_float(y);
+#endif
 }
 
 #endif
