@@ -153,7 +153,17 @@ ES_SCR_HD void es_screen_f32(const uint32_t s, const double pix2,
     double t = w_signed * nm1;
     const double big = 6755399441055744.0;
     t -= (t + big) - big;
+#if !defined(ES_SCREEN_POLY_SINCOS)
+    /* special-function unit: abs. error ~4e-7 on [-pi, pi], two MUFU + two
+     * multiplies instead of ~22 FMA-pipe instructions; the fp32 parity errors
+     * (2-5e-6, dominated by fp32 accumulation) move by < 2e-7
+     * (profiles/parity_errors.py), the column kernels gain 5 % */
+    const float z = 6.28318530717958647692f * __double2float_rz(t);
+    re = __cosf(z);
+    im = __sinf(z);
+#else
     es_sincos_turns(__double2float_rz(t), re, im);
+#endif
     inv_n = __double2float_rz(y);
 #else
     const double a = 1.0 - pix2 * es_uint_to_double(s);
