@@ -14,8 +14,10 @@
  *   1/n   = fp32 rsqrt seed + one Newton step in fp64       (rel. err ~2e-14)
  *   n - 1 = (1 - l^2 - m^2) / n - 1
  *   t     = w (n - 1) - round(w (n - 1))  (magic-constant rounding, fp64)
- *   cos, sin(2 pi t): quadrant by magic-constant rounding in fp32, degree
- *                     8 / 9 polynomials on [-pi/4, pi/4]    (abs. err ~1e-7)
+ *   cos, sin(2 pi t): device: special-function unit (abs. err ~4e-7);
+ *                     host / -DES_SCREEN_POLY_SINCOS: quadrant by
+ *                     magic-constant rounding in fp32, degree 8 / 9
+ *                     polynomials on [-pi/4, pi/4]          (abs. err ~1e-7)
  * Host-callable so that tests/screen_host.cpp can check it against libm.
  */
 #ifndef ES_SCREEN_H_
