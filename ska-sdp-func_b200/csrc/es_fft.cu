@@ -43,6 +43,7 @@
 #include "es_fft_plan.h"
 #include "es_screen.h"
 
+#define ES_FFT_COL_GROUP 8 /* degridding column pass: bundles per CTA group */
 #define ES_FFT_THREADS 512 /* upper bound of the CTA size (128 registers each) */
 #define ES_FFT_MAX_SMEM (227 * 1024 - 512) /* 512 B of static occupancy flags */
 
@@ -570,8 +571,18 @@ __global__ void __launch_bounds__(ES_FFT_THREADS, 1) es_fft_degrid_cols_kernel(
     const T2* tw = lay.cols_twg ? tw_g :
             x + ((size_t) lay.cols_pitch << lay.lshift);
     const int gsz = pl.n, n = g.image_size;
-    const int q = blockIdx.x % nplanes;
-    const int col0 = (blockIdx.x / nplanes) << lay.lshift;
+    /* CTA order: groups of ES_FFT_COL_GROUP adjacent column bundles, all
+     * planes of a group before the next group. Adjacent bundles of one plane
+     * run together (their 16 / 32-byte pieces complete whole lines in L2
+     * before eviction) and the group's image columns stay in L2 across the
+     * planes of the batch. */
+    const int nbundles = n >> lay.lshift;
+    const int grp = blockIdx.x / (ES_FFT_COL_GROUP * nplanes);
+    const int rem = blockIdx.x - grp * (ES_FFT_COL_GROUP * nplanes);
+    const int q = rem / ES_FFT_COL_GROUP;
+    const int bundle = grp * ES_FFT_COL_GROUP + (rem - q * ES_FFT_COL_GROUP);
+    if (bundle >= nbundles) return;
+    const int col0 = bundle << lay.lshift;
     /* only the tile rows the gather reads are stored; none: nothing to do */
     if (!occ_fetch(s_bits, occ_plane(occ, lay, q) + lay.ntile * lay.occ_nw,
             lay.occ_nw)) return;
@@ -940,7 +951,9 @@ int es_fft_degrid_cols(const EsFft* f, const EsGeom* g, const void* image_t,
     cudaStream_t s = (cudaStream_t) stream;
     const EsFftLayout lay = fft_layout(f);
     const EsFftCfg& c = f->cols;
-    dim3 grid((unsigned) ((f->image_size >> c.lshift) * nplanes));
+    const int nbundles = f->image_size >> c.lshift;
+    const int groups = (nbundles + ES_FFT_COL_GROUP - 1) / ES_FFT_COL_GROUP;
+    dim3 grid((unsigned) (groups * ES_FFT_COL_GROUP * nplanes));
     if (f->is_double)
         es_fft_degrid_cols_kernel<double><<<grid, c.threads, c.smem_bytes,
                 s>>>(f->line, (const double2*) f->d_tw, f->d_bpos, *g,
