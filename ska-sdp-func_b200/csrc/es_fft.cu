@@ -43,7 +43,7 @@
 #include "es_fft_plan.h"
 #include "es_screen.h"
 
-#define ES_FFT_COL_GROUP 8 /* degridding column pass: bundles per CTA group */
+#define ES_FFT_COL_GROUP 16 /* degridding column pass: bundles per CTA group */
 #define ES_FFT_THREADS 512 /* upper bound of the CTA size (128 registers each) */
 #define ES_FFT_MAX_SMEM (227 * 1024 - 512) /* 512 B of static occupancy flags */
 
