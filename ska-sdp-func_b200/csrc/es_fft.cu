@@ -801,7 +801,9 @@ int es_fft_create(int grid_size, int image_size, int is_double, EsFft** out)
      * in shared memory (32-byte pieces of the row-major intermediate) */
     int e[4] = {0, 0, is_double ? 1 : 2, is_double ? 0 : 1};
     const char* env = getenv("SKA_SDP_FUNC_ES_FFT_CFG");
-    if (env) (void) sscanf(env, "%d,%d,%d,%d", &e[0], &e[1], &e[2], &e[3]);
+    int rows_forced = 0;
+    if (env) rows_forced = sscanf(env, "%d,%d,%d,%d", &e[0], &e[1], &e[2],
+            &e[3]) == 4;
     if (e[3] < 0 || e[3] > 2) e[3] = 0;
     for (int k = 0; k < 2; ++k)
         if (e[k] < 0 || e[k] > ES_FFT_THREADS || (e[k] & 31)) e[k] = 0;
@@ -811,8 +813,13 @@ int es_fft_create(int grid_size, int image_size, int is_double, EsFft** out)
     for (;; --rshift)
     {
         make_cfg(&f->line, cplx, rshift, e[0], &f->rows);
-        if ((f->rows.smem_bytes <= ES_FFT_MAX_SMEM &&
-                grid_size % (1 << rshift) == 0) || rshift == 0) break;
+        /* default: a row bundle only where two CTAs still fit on an SM (C5:
+         * 2 rows of 11520 leave one 512-thread CTA: rows 1365 vs 1314 ms);
+         * a bundle forced by the environment only has to fit */
+        const size_t need = rows_forced ? f->rows.smem_bytes :
+                2 * (f->rows.smem_bytes + 1024);
+        if ((need <= ES_FFT_MAX_SMEM && grid_size % (1 << rshift) == 0) ||
+                rshift == 0) break;
     }
     int lshift = e[2];
     for (;; --lshift)
