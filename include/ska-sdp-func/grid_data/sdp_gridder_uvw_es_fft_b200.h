@@ -86,6 +86,15 @@ void sdp_gridder_uvw_es_fft_enable_timing(sdp_GridderUvwEsFft* plan,
 void sdp_gridder_uvw_es_fft_get_stats(const sdp_GridderUvwEsFft* plan,
         sdp_EsCallStats* stats);
 
+/* Device time of every w-plane batch of the last grid / degrid call (timing
+ * enabled): batch k covered planes [first_plane[k], first_plane[k] +
+ * num_planes[k]) and took ms[k]. Returns the number of batches written (at
+ * most capacity). A caller that shards the lattice over several GPUs uses
+ * these as measured per-plane costs to balance plane ownership. */
+int32_t sdp_gridder_uvw_es_fft_get_batch_times(
+        const sdp_GridderUvwEsFft* plan, int32_t capacity,
+        int32_t* first_plane, int32_t* num_planes, double* ms);
+
 #ifdef __cplusplus
 }
 #endif

@@ -24,6 +24,12 @@ __global__ void __launch_bounds__(256) rate_kernel(float2* out, float2 a, float2
             if (MODE == 3) v[c] = __fadd2_rn(v[c], a);
             if (MODE == 4) { v[c].x = v[c].x * a.x; v[c].y = v[c].y * a.y; }
             if (MODE == 5) v[c] = __fmul2_rn(v[c], a);
+            /* complex multiply by (a.x, a.y), interleaved (re, im) layout */
+            if (MODE == 6) { const float2 t = v[c];
+                v[c].x = fmaf(t.x, a.x, -t.y * a.y); v[c].y = fmaf(t.x, a.y, t.y * a.x); }
+            if (MODE == 7) { const float2 t = v[c];
+                v[c] = __ffma2_rn(t, make_float2(a.x, a.x),
+                        __fmul2_rn(make_float2(t.y, t.x), make_float2(-a.y, a.y))); }
         }
     }
     float2 s = v[0];
@@ -59,5 +65,8 @@ int main()
     run<3>("FADD2", out, p.multiProcessorCount, hz);
     run<4>("FMUL", out, p.multiProcessorCount, hz);
     run<5>("FMUL2", out, p.multiProcessorCount, hz);
+    // per chain step: 4 scalar instructions / 2 packed instructions (counted as 2 "scalar ops" like the rest)
+    run<6>("CMUL", out, p.multiProcessorCount, hz);
+    run<7>("CMUL2", out, p.multiProcessorCount, hz);
     return 0;
 }

@@ -15,6 +15,7 @@ extern "C" {
 #endif
 
 #define ES_TILE 64 /* uv tile edge in grid cells; must be >= support + 1 */
+#define ES_MAX_DEVICES 64 /* per-device launch configuration caches */
 
 /* Geometry shared by all kernels (doubles: coordinates are always fp64). */
 typedef struct EsGeom
@@ -66,18 +67,14 @@ int es_launch_tile_bounds(const EsGeom* g, const uint64_t* keys,
 
 /* Build the sorted records. vis/weight non-NULL: scatter records carrying the
  * weighted (conjugated if w < 0) visibility; NULL: gather records carrying
- * the flip sign. */
+ * the flip sign. entry_pos non-NULL (degridding): entry_pos[offsets[i] + k] =
+ * sorted position of the k-th entry of visibility i. */
 int es_launch_build_records(const EsGeom* g, const void* uvw, const void* freq,
         const void* vis, const void* weight, const uint64_t* keys,
         const uint32_t* vals, int64_t num_entries, void* records,
-        es_stream_t stream);
+        const uint32_t* offsets, uint32_t* entry_pos, es_stream_t stream);
 
 /* ---- per batch of resident w-planes [first_plane, first_plane + nplanes) ---- */
-
-/* Gridding: write every cell of the nplanes planes (zero where empty). */
-int es_launch_scatter(const EsGeom* g, const void* records,
-        const uint64_t* keys, const uint32_t* tile_start, int first_plane,
-        int nplanes, void* planes, es_stream_t stream);
 
 /* dirty += sum_planes Re(plane_centre * w-screen) (after the inverse FFT). */
 int es_launch_apply_screen(const EsGeom* g, const void* planes,
@@ -87,14 +84,11 @@ int es_launch_apply_screen(const EsGeom* g, const void* planes,
 int es_launch_reverse_screen(const EsGeom* g, const void* dirty,
         int first_plane, int nplanes, void* planes, es_stream_t stream);
 
-/* Degridding: acc[entry] += sum_cells plane * kernel for the batch. */
-int es_launch_gather(const EsGeom* g, const void* records,
-        const uint64_t* keys, const uint32_t* tile_start, int first_plane,
-        int nplanes, const void* planes, void* acc, es_stream_t stream);
-
-/* vis[index] += acc[entry] (imag * flip) over all entries. */
+/* vis[i] += sum over the entries of visibility i, in entry order, of
+ * acc[entry] (imag * flip): one thread per visibility, bitwise reproducible. */
 int es_launch_finish_degrid(const EsGeom* g, const void* records,
-        const void* acc, int64_t num_entries, void* vis, es_stream_t stream);
+        const void* acc, const uint32_t* offsets, const uint32_t* entry_pos,
+        int64_t num_entries, void* vis, es_stream_t stream);
 
 /* ---- once per call ---- */
 

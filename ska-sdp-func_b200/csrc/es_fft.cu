@@ -871,8 +871,10 @@ int es_fft_create(int grid_size, int image_size, int is_double, EsFft** out)
                 sizeof(int32_t) * (size_t) nb, cudaMemcpyHostToDevice);
     }
     free(tw); free(bpos); free(tw_t);
-    const size_t sm = f->rows.smem_bytes > f->cols.smem_bytes ?
-            f->rows.smem_bytes : f->cols.smem_bytes;
+    /* The dynamic shared-memory limit belongs to the function and the
+     * device, not to this plan: always opt in to the maximum any plan can
+     * ask for, so that plans of different sizes can be alive together. */
+    const size_t sm = ES_FFT_MAX_SMEM;
     if (!err && is_double)
     {
         err = fft_set_smem(es_fft_grid_rows_kernel<double>, sm);

@@ -86,6 +86,9 @@ struct sdp_GridderUvwEsFft
     int32_t stats_pending; /* 1 grid / 2 degrid timings not yet collected */
     cudaEvent_t* stage_ev; /* 4 per plane batch when timing is enabled */
     int32_t stage_cap, stage_used;
+    int32_t* batch_first;  /* first plane / plane count of every batch of the */
+    int32_t* batch_count;  /* last call (timing enabled), stage_ev[4 k ..] */
+    int32_t batch_cap, batch_used;
 };
 
 /* ------------------------------------------------------------ utilities */
@@ -340,6 +343,8 @@ void sdp_gridder_uvw_es_fft_free_plan(sdp_GridderUvwEsFft* plan)
     for (int k = 0; k < plan->stage_cap; ++k)
         (void) cudaEventDestroy(plan->stage_ev[k]);
     free(plan->stage_ev);
+    free(plan->batch_first);
+    free(plan->batch_count);
     free(plan);
 }
 
@@ -412,12 +417,15 @@ sdp_GridderUvwEsFft* sdp_gridder_uvw_es_fft_create_plan(
     if (*status) return 0;
     const int64_t rows = sdp_mem_shape_dim(vis, 0);
     const int64_t chans = sdp_mem_shape_dim(vis, 1);
-    if (rows * chans >= 2147483647LL)
+    if (rows * chans >= (1LL << 30))
     {
-        /* same limit as the reference's 32-bit i_vis (kernels.cu:150-152) */
+        /* The reference's limit is its 32-bit i_vis, 2^31 (kernels.cu:150-
+         * 152). Here a visibility expands into up to 4 tile records whose
+         * offsets and total are kept in 32 bits, and the sort values carry
+         * the entry number in their two top bits: 2^30. */
         *status = SDP_ERR_INVALID_ARGUMENT;
         SDP_LOG_ERROR("Too many visibilities for one plan (rows x channels "
-                "must be below 2^31).");
+                "must be below 2^30).");
         return 0;
     }
 
@@ -585,6 +593,32 @@ void sdp_gridder_uvw_es_fft_get_stats(const sdp_GridderUvwEsFft* plan_,
     }
     plan->stats_pending = 0;
     *stats = plan->stats;
+}
+
+int32_t sdp_gridder_uvw_es_fft_get_batch_times(
+        const sdp_GridderUvwEsFft* plan_, int32_t capacity,
+        int32_t* first_plane, int32_t* num_planes, double* ms)
+{
+    sdp_GridderUvwEsFft* plan = (sdp_GridderUvwEsFft*) plan_;
+    if (!plan || !plan->timing || !plan->have_events) return 0;
+    if (plan->stats_pending)
+    {
+        sdp_EsCallStats unused;
+        sdp_gridder_uvw_es_fft_get_stats(plan, &unused); /* waits for the call */
+    }
+    int32_t n = 0;
+    for (int k = 0; k < plan->batch_used && 4 * k + 3 < plan->stage_used &&
+            n < capacity; ++k, ++n)
+    {
+        float t = 0.0f;
+        if (cudaEventElapsedTime(&t, plan->stage_ev[4 * k],
+                plan->stage_ev[4 * k + 3]) != cudaSuccess)
+            (void) cudaGetLastError();
+        if (first_plane) first_plane[n] = plan->batch_first[k];
+        if (num_planes) num_planes[n] = plan->batch_count[k];
+        if (ms) ms[n] = (double) t;
+    }
+    return n;
 }
 
 /* ----------------------------------------------------------------- FFT */
@@ -864,10 +898,15 @@ static void presort(sdp_GridderUvwEsFft* plan, const EsArrays* a,
             &sort_bytes, s));
     ES_CUDA(es_launch_tile_bounds(g, (const uint64_t*) plan->keys_b.ptr, m,
             (uint32_t*) plan->tile_start.ptr, s));
+    /* degridding: the sort input values are dead now; their buffer takes the
+     * sorted position of every entry (entry_pos, used by the final
+     * per-visibility sum) */
     ES_CUDA(es_launch_build_records(g, a->uvw, a->freq,
             for_gridding ? a->vis : 0, for_gridding ? a->weight : 0,
             (const uint64_t*) plan->keys_b.ptr,
-            (const uint32_t*) plan->vals_b.ptr, m, plan->records.ptr, s));
+            (const uint32_t*) plan->vals_b.ptr, m, plan->records.ptr,
+            (const uint32_t*) plan->offsets.ptr,
+            for_gridding ? 0 : (uint32_t*) plan->vals_a.ptr, s));
     plan->stats.kernel_launches += 3;
     *num_entries = m;
 }
@@ -910,6 +949,17 @@ static void work_reserve(sdp_GridderUvwEsFft* plan, int nb, int64_t m,
         buffer_reserve(&plan->partials, (size_t) lim->max_partials * tile_bytes, status);
 }
 
+/* Planes per batch for an owned range of `count` planes: as few batches as
+ * the resident capacity allows, all of (nearly) the same size, so that a
+ * range of e.g. 25 planes with 12 resident runs as 9 + 8 + 8 and not as
+ * 12 + 12 + 1 (the line-FFT kernels fill the device per launch). */
+static int even_batch(const sdp_GridderUvwEsFft* plan, int count)
+{
+    if (count <= plan->plane_batch) return count > 0 ? count : 1;
+    const int nbatches = (count + plan->plane_batch - 1) / plan->plane_batch;
+    return (count + nbatches - 1) / nbatches;
+}
+
 /* --------------------------------------------------------------- timing */
 
 static void events_begin(sdp_GridderUvwEsFft* plan)
@@ -919,6 +969,7 @@ static void events_begin(sdp_GridderUvwEsFft* plan)
     plan->stats.timing_enabled = plan->timing;
     plan->stats.pruned_fft = plan->pruned_fft ? 1 : 0;
     plan->stage_used = 0;
+    plan->batch_used = 0;
     if (plan->timing && !plan->have_events)
     {
         int ok = 1;
@@ -955,6 +1006,27 @@ static void stage_mark(sdp_GridderUvwEsFft* plan)
         plan->stage_cap = cap;
     }
     (void) cudaEventRecord(plan->stage_ev[plan->stage_used++], plan->stream);
+}
+
+/* Remembers which planes the batch whose four stage events follow covers. */
+static void batch_mark(sdp_GridderUvwEsFft* plan, int first, int count)
+{
+    if (!plan->timing) return;
+    if (plan->batch_used == plan->batch_cap)
+    {
+        const int cap = plan->batch_cap ? 2 * plan->batch_cap : 64;
+        int32_t* f = (int32_t*) realloc(plan->batch_first,
+                sizeof(int32_t) * (size_t) cap);
+        if (f) plan->batch_first = f;
+        int32_t* c = (int32_t*) realloc(plan->batch_count,
+                sizeof(int32_t) * (size_t) cap);
+        if (c) plan->batch_count = c;
+        if (!f || !c) return;
+        plan->batch_cap = cap;
+    }
+    plan->batch_first[plan->batch_used] = first;
+    plan->batch_count[plan->batch_used] = count;
+    plan->batch_used++;
 }
 
 /* stage order: grid = scatter, fft, screen; degrid = screen, fft, gather */
@@ -1028,11 +1100,12 @@ void sdp_grid_uvw_es_fft(sdp_GridderUvwEsFft* plan, const sdp_Mem* uvw,
     if (*status) return;
     event_mark(plan, 1);
 
-    for (int first = g->plane_begin; first < g->plane_end;
-            first += plan->plane_batch)
+    const int batch = even_batch(plan, g->plane_end - g->plane_begin);
+    for (int first = g->plane_begin; first < g->plane_end; first += batch)
     {
         int nb = g->plane_end - first;
-        if (nb > plan->plane_batch) nb = plan->plane_batch;
+        if (nb > batch) nb = batch;
+        batch_mark(plan, first, nb);
         stage_mark(plan);
         /* pruned mode: only occupied tiles are written / transformed */
         if (plan->pruned_fft)
@@ -1150,11 +1223,12 @@ void sdp_ifft_degrid_uvw_es(sdp_GridderUvwEsFft* plan, const sdp_Mem* uvw,
                 g->image_size, g->is_double, 0, s));
         plan->stats.kernel_launches += 1;
     }
-    for (int first = g->plane_begin; first < g->plane_end;
-            first += plan->plane_batch)
+    const int batch = even_batch(plan, g->plane_end - g->plane_begin);
+    for (int first = g->plane_begin; first < g->plane_end; first += batch)
     {
         int nb = g->plane_end - first;
-        if (nb > plan->plane_batch) nb = plan->plane_batch;
+        if (nb > batch) nb = batch;
+        batch_mark(plan, first, nb);
         stage_mark(plan);
         if (plan->pruned_fft)
         {
@@ -1192,8 +1266,9 @@ void sdp_ifft_degrid_uvw_es(sdp_GridderUvwEsFft* plan, const sdp_Mem* uvw,
     }
     event_mark(plan, 2);
     late_copy_wait(plan, &a);
-    ES_CUDA(es_launch_finish_degrid(g, plan->records.ptr, plan->acc.ptr, m,
-            a.vis, s));
+    ES_CUDA(es_launch_finish_degrid(g, plan->records.ptr, plan->acc.ptr,
+            (const uint32_t*) plan->offsets.ptr,
+            (const uint32_t*) plan->vals_a.ptr, m, a.vis, s));
     plan->stats.kernel_launches += 1;
     if (a.staged)
     {

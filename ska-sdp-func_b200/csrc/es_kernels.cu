@@ -10,13 +10,12 @@
  *               its footprint overlaps; records are radix sorted by
  *               (tile, first owned w-plane), so the records that touch plane p
  *               of tile t are ONE contiguous range found by binary search;
- *   scatter   - one CTA per (tile, plane): the tile is accumulated in shared
- *               memory without atomics (each warp owns a band of 16 rows, the
- *               lanes of a warp own distinct cells of one footprint) and then
- *               flushed once with coalesced 16-byte stores. Every cell of the
- *               plane is written exactly once, so the reference's per-plane
- *               cudaMemset (es_fft.cpp:586) disappears;
- *   gather    - the same ranges, one thread per record, plain loads;
+ *   scatter   - es_scatter.cu: load-balanced (tile, plane) work units, the
+ *               tile accumulated in shared memory without atomics and
+ *               flushed once, so the reference's per-plane cudaMemset
+ *               (es_fft.cpp:586) disappears;
+ *   gather    - the same ranges as (tile, record slice) units, one thread per
+ *               record, plain loads;
  *   w-screen  - one thread per 4 mirror pixels as in kernels.cu:429-679, but
  *               looping over a BATCH of resident planes with register
  *               accumulators (one image read-modify-write per batch), and with
@@ -35,6 +34,8 @@
 
 #define ES_C0 299792458.0           /* kernels.cu:159 */
 #define ES_PI 3.1415926535897931    /* kernels.cu:10 */
+#define ES_VIS_BITS 30              /* sort values: visibility index | entry number << 30 */
+#define ES_VIS_MASK ((1u << ES_VIS_BITS) - 1u)
 
 using namespace es;
 
@@ -123,13 +124,16 @@ __global__ void __launch_bounds__(256) es_emit_entries_kernel(EsGeom g,
     const int half = g.grid_size / 2;
     const uint64_t pk = (uint64_t) (g.plane_end - g.plane_begin);
     const uint64_t kp = (uint64_t) (f.p_lo - g.plane_begin);
-    uint32_t slot = offsets[i];
+    const uint32_t first_slot = offsets[i];
+    uint32_t slot = first_slot;
     for (int tu = (f.u_lo + half) / ES_TILE; tu <= (f.u_hi + half) / ES_TILE; ++tu)
     {
         for (int tv = (f.v_lo + half) / ES_TILE; tv <= (f.v_hi + half) / ES_TILE; ++tv)
         {
             keys[slot] = (uint64_t) (tu * g.ntile + tv) * pk + kp;
-            vals[slot] = (uint32_t) i;
+            /* visibility index (< 2^30, checked at plan creation) and, in the
+             * two top bits, the number of this entry within the visibility */
+            vals[slot] = (uint32_t) i | ((slot - first_slot) << ES_VIS_BITS);
             ++slot;
         }
     }
@@ -167,11 +171,15 @@ __global__ void __launch_bounds__(256) es_build_records_kernel(EsGeom g,
         const typename Prec<T>::T2* __restrict__ vis,
         const T* __restrict__ weight, const uint64_t* __restrict__ keys,
         const uint32_t* __restrict__ vals, int64_t num_entries,
-        typename Prec<T>::Rec* __restrict__ records)
+        typename Prec<T>::Rec* __restrict__ records,
+        const uint32_t* __restrict__ offsets, uint32_t* __restrict__ entry_pos)
 {
     const int64_t e = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= num_entries) return;
-    const uint32_t idx = vals[e];
+    const uint32_t idx = vals[e] & ES_VIS_MASK;
+    /* degridding: where the k-th entry of visibility idx went in the sort */
+    if (entry_pos)
+        entry_pos[offsets[idx] + (vals[e] >> ES_VIS_BITS)] = (uint32_t) e;
     const int row = (int) (idx / (uint32_t) g.num_chan);
     const int chan = (int) (idx % (uint32_t) g.num_chan);
     const Foot f = es_footprint<T>(g, uvw, freq, row, chan);
@@ -213,133 +221,6 @@ __global__ void __launch_bounds__(256) es_plane_histogram_kernel(EsGeom g,
     const Foot f = es_footprint<T>(g, uvw, freq, row, chan);
     if (!f.valid) return;
     atomicAdd(&hist[f.p_lo], 1ULL);
-}
-
-/* ------------------------------------------------------------- scatter */
-
-#define ES_SCATTER_THREADS 128
-#define ES_BAND (ES_TILE / (ES_SCATTER_THREADS / 32)) /* rows owned per warp */
-
-/* CS: column slots per row step (16: two rows per step, support <= 15;
- * 32: one row per step, support 16). */
-template<typename T, int CS>
-__global__ void __launch_bounds__(ES_SCATTER_THREADS) es_scatter_kernel(
-        EsGeom g, const typename Prec<T>::Rec* __restrict__ records,
-        const uint64_t* __restrict__ keys,
-        const uint32_t* __restrict__ tile_start, int first_plane,
-        typename Prec<T>::T2* __restrict__ planes)
-{
-    typedef typename Prec<T>::T2 T2;
-    typedef typename Prec<T>::Rec Rec;
-    extern __shared__ __align__(16) unsigned char es_smem[];
-    T2* tile = (T2*) es_smem; /* [ES_TILE][ES_TILE] */
-    __shared__ int s_pos[ES_SCATTER_THREADS];
-    __shared__ T s_du[ES_SCATTER_THREADS], s_dv[ES_SCATTER_THREADS];
-    __shared__ T s_vre[ES_SCATTER_THREADS], s_vim[ES_SCATTER_THREADS];
-
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int tile_id = blockIdx.x;
-    const int plane = first_plane + blockIdx.y;
-    const int tu = tile_id / g.ntile, tv = tile_id % g.ntile;
-    const int gsz = g.grid_size;
-    const int rows_valid = min(ES_TILE, gsz - tu * ES_TILE);
-    const int cols_valid = min(ES_TILE, gsz - tv * ES_TILE);
-    T2* out = planes + (size_t) blockIdx.y * gsz * gsz +
-            (size_t) (tu * ES_TILE) * gsz + (size_t) (tv * ES_TILE);
-
-    uint32_t a, b;
-    es_entry_range(g, keys, tile_start, tile_id, plane, plane, a, b);
-
-    /* 16-byte vectors of the tile rows: VEC cells each. */
-    constexpr int VEC = 16 / (int) sizeof(T2);
-    constexpr int VPR = ES_TILE / VEC; /* vectors per tile row */
-    const int vec_valid = cols_valid / VEC; /* grid_size is even */
-
-    if (a == b)
-    {
-        /* nothing lands here on this plane: the fused "memset" */
-        const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
-        for (int v = tid; v < ES_TILE * VPR; v += ES_SCATTER_THREADS)
-        {
-            const int r = v / VPR, c = v % VPR;
-            if (r < rows_valid && c < vec_valid)
-                *reinterpret_cast<float4*>(out + (size_t) r * gsz + c * VEC) = zero;
-        }
-        return;
-    }
-
-    for (int v = tid; v < ES_TILE * VPR; v += ES_SCATTER_THREADS)
-        reinterpret_cast<float4*>(tile)[v] = make_float4(0.f, 0.f, 0.f, 0.f);
-    __syncthreads();
-
-    const int w_sup = g.support;
-    const T beta = (T) g.beta;
-    const T inv_hs = (T) (2.0 / (double) w_sup);
-    const int band_lo = warp * ES_BAND;
-    const int band_hi = min(band_lo + ES_BAND, rows_valid) - 1;
-    const int c = lane % CS;       /* my column slot */
-    const int rsub = lane / CS;    /* my row within a step */
-    constexpr int RPS = 32 / CS;   /* rows per step */
-
-    for (uint32_t chunk = a; chunk < b; chunk += ES_SCATTER_THREADS)
-    {
-        const int n = (int) min((uint32_t) ES_SCATTER_THREADS, b - chunk);
-        if (tid < n)
-        {
-            const Rec r = records[chunk + tid];
-            const int dp = plane - r.p0;
-            /* kernels.cu:219-221; dp > W cannot carry weight */
-            const T kw = (dp >= 0 && dp <= w_sup) ?
-                    es_psi(beta, ((T) dp + r.dw) * inv_hs) : (T) 0;
-            s_pos[tid] = ((int) r.lu0 << 16) | ((int) r.lv0 & 0xffff);
-            s_du[tid] = r.du;
-            s_dv[tid] = r.dv;
-            s_vre[tid] = r.vre * kw;
-            s_vim[tid] = r.vim * kw;
-        }
-        __syncthreads();
-        for (int e = 0; e < n; ++e)
-        {
-            const int pos = s_pos[e];
-            const int lu0 = pos >> 16;
-            const int r_lo = max(lu0, band_lo);
-            const int r_hi = min(lu0 + w_sup, band_hi);
-            if (r_lo > r_hi) continue; /* warp-uniform */
-            const int lv0 = (int) (short) (pos & 0xffff);
-            const int col = lv0 + c;
-            const bool col_ok = (c <= w_sup) && col >= 0 && col < cols_valid;
-            /* kernels.cu:201-213: one u weight per lane 0..W, one v weight
-             * per column slot */
-            const T ku_lane = (lane <= w_sup) ?
-                    es_psi(beta, ((T) lane + s_du[e]) * inv_hs) : (T) 0;
-            T kvc = col_ok ? es_psi(beta, ((T) c + s_dv[e]) * inv_hs) : (T) 0;
-            if (col & 1) kvc = -kvc; /* (-1)^(gu+gv), kernels.cu:233-235 */
-            const T pre = s_vre[e] * kvc, pim = s_vim[e] * kvc;
-            for (int r0 = r_lo; r0 <= r_hi; r0 += RPS)
-            {
-                const int r = r0 + rsub;
-                T ku = __shfl_sync(0xffffffffu, ku_lane, min(r - lu0, 31));
-                if (r & 1) ku = -ku;
-                if (col_ok && r <= r_hi)
-                {
-                    T2 cell = tile[r * ES_TILE + col];
-                    cell.x += pre * ku;
-                    cell.y += pim * ku;
-                    tile[r * ES_TILE + col] = cell;
-                }
-            }
-            __syncwarp();
-        }
-        __syncthreads();
-    }
-
-    for (int v = tid; v < ES_TILE * VPR; v += ES_SCATTER_THREADS)
-    {
-        const int r = v / VPR, cv = v % VPR;
-        if (r < rows_valid && cv < vec_valid)
-            *reinterpret_cast<float4*>(out + (size_t) r * gsz + cv * VEC) =
-                    reinterpret_cast<const float4*>(tile)[v];
-    }
 }
 
 /* -------------------------------------------------------------- gather */
@@ -432,24 +313,6 @@ __device__ __forceinline__ void es_gather_range(const EsGeom& g,
     }
 }
 
-/* One CTA per uv tile (cuFFT fallback path). */
-template<typename T, int NS>
-__global__ void __launch_bounds__(ES_GATHER_THREADS) es_gather_kernel(
-        EsGeom g, const typename Prec<T>::Rec* __restrict__ records,
-        const uint64_t* __restrict__ keys,
-        const uint32_t* __restrict__ tile_start, int first_plane, int nplanes,
-        const typename Prec<T>::T2* __restrict__ planes,
-        typename Prec<T>::T2* __restrict__ acc)
-{
-    const int tile_id = blockIdx.x;
-    uint32_t a, b;
-    es_entry_range(g, keys, tile_start, tile_id, first_plane,
-            first_plane + nplanes - 1, a, b);
-    if (a == b) return;
-    es_gather_range<T, NS>(g, records, tile_id, a, b, first_plane, nplanes,
-            planes, acc);
-}
-
 /* Load-balanced form: persistent CTAs pull (tile, record slice) units from
  * the list of es_work_plan_kernel (per_plane = 0). Real uv coverage is very
  * uneven (a Mid- or Low-like core puts ~10 % of all records into one tile):
@@ -478,20 +341,35 @@ __global__ void __launch_bounds__(ES_GATHER_THREADS) es_gather2_kernel(
     }
 }
 
+/* vis[i] += sum of the partial sums of visibility i's (at most 4) tile
+ * entries, taken in entry order: one thread per visibility, no atomics, so
+ * degridded visibilities are bitwise reproducible (kernels.cu:267-268 adds
+ * the one sum of its one thread the same way). */
 template<typename T>
 __global__ void __launch_bounds__(256) es_finish_degrid_kernel(
         const typename Prec<T>::Rec* __restrict__ records,
-        const typename Prec<T>::T2* __restrict__ acc, int64_t num_entries,
-        T* __restrict__ vis)
+        const typename Prec<T>::T2* __restrict__ acc,
+        const uint32_t* __restrict__ offsets,
+        const uint32_t* __restrict__ entry_pos, int64_t num_vis,
+        typename Prec<T>::T2* __restrict__ vis)
 {
-    const int64_t e = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
-    if (e >= num_entries) return;
-    const typename Prec<T>::T2 t = acc[e];
-    const size_t idx = records[e].idx;
-    const T flip = records[e].vre;
-    /* kernels.cu:267-268 */
-    atomicAdd(&vis[2 * idx], t.x);
-    atomicAdd(&vis[2 * idx + 1], t.y * flip);
+    const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= num_vis) return;
+    const uint32_t lo = offsets[i], hi = offsets[i + 1];
+    if (lo == hi) return;
+    T sx = 0, sy = 0, flip = 1;
+    for (uint32_t k = lo; k < hi; ++k)
+    {
+        const uint32_t e = entry_pos[k];
+        const typename Prec<T>::T2 t = acc[e];
+        if (k == lo) flip = records[e].vre;
+        sx += t.x;
+        sy += t.y;
+    }
+    typename Prec<T>::T2 v = vis[i];
+    v.x += sx;
+    v.y += sy * flip;
+    vis[i] = v;
 }
 
 /* ------------------------------------------------------------ w-screen */
@@ -692,28 +570,6 @@ inline unsigned int blocks_for(int64_t n, int threads)
     return (unsigned int) ((n + threads - 1) / threads);
 }
 
-template<typename T, int CS>
-static int launch_scatter_t(const EsGeom* g, const void* records,
-        const uint64_t* keys, const uint32_t* tile_start, int first_plane,
-        int nplanes, void* planes, cudaStream_t s)
-{
-    typedef typename Prec<T>::T2 T2;
-    typedef typename Prec<T>::Rec Rec;
-    const size_t smem = (size_t) ES_TILE * ES_TILE * sizeof(T2);
-    static bool configured = false;
-    if (!configured)
-    {
-        cudaError_t err = cudaFuncSetAttribute(es_scatter_kernel<T, CS>,
-                cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
-        if (err != cudaSuccess) return (int) err;
-        configured = true;
-    }
-    dim3 grid((unsigned) (g->ntile * g->ntile), (unsigned) nplanes);
-    es_scatter_kernel<T, CS><<<grid, ES_SCATTER_THREADS, smem, s>>>(*g,
-            (const Rec*) records, keys, tile_start, first_plane, (T2*) planes);
-    return (int) cudaGetLastError();
-}
-
 template<typename T, int NS>
 static int launch_gather2_ts(const EsGeom* g, const void* records,
         const void* units, uint32_t* counters, int first_plane, int nplanes,
@@ -721,41 +577,28 @@ static int launch_gather2_ts(const EsGeom* g, const void* records,
 {
     typedef typename Prec<T>::T2 T2;
     typedef typename Prec<T>::Rec Rec;
-    static int grid_size = 0;
+    /* persistent grid, per device */
+    static int grid_sizes[ES_MAX_DEVICES];
+    int dev = 0;
+    cudaError_t err = cudaGetDevice(&dev);
+    if (err != cudaSuccess) return (int) err;
+    if (dev < 0 || dev >= ES_MAX_DEVICES) return (int) cudaErrorInvalidDevice;
+    int grid_size = __atomic_load_n(&grid_sizes[dev], __ATOMIC_ACQUIRE);
     if (grid_size == 0)
     {
-        int dev = 0, sms = 0, per_sm = 0;
-        cudaError_t err = cudaGetDevice(&dev);
-        if (err == cudaSuccess) err = cudaDeviceGetAttribute(&sms,
-                cudaDevAttrMultiProcessorCount, dev);
+        int sms = 0, per_sm = 0;
+        err = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount,
+                dev);
         if (err == cudaSuccess) err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(
                 &per_sm, es_gather2_kernel<T, NS>, ES_GATHER_THREADS, 0);
         if (err != cudaSuccess) return (int) err;
         if (per_sm < 1) per_sm = 1;
         grid_size = sms * per_sm;
+        __atomic_store_n(&grid_sizes[dev], grid_size, __ATOMIC_RELEASE);
     }
     es_gather2_kernel<T, NS><<<grid_size, ES_GATHER_THREADS, 0, s>>>(*g,
             (const Rec*) records, (const EsUnit*) units, counters, first_plane,
             nplanes, (const T2*) planes, (T2*) acc);
-    return (int) cudaGetLastError();
-}
-
-template<typename T>
-static int launch_gather_t(const EsGeom* g, const void* records,
-        const uint64_t* keys, const uint32_t* tile_start, int first_plane,
-        int nplanes, const void* planes, void* acc, cudaStream_t s)
-{
-    typedef typename Prec<T>::T2 T2;
-    typedef typename Prec<T>::Rec Rec;
-    dim3 grid((unsigned) (g->ntile * g->ntile));
-    if (g->support + 1 <= 9)
-        es_gather_kernel<T, 9><<<grid, ES_GATHER_THREADS, 0, s>>>(*g,
-                (const Rec*) records, keys, tile_start, first_plane, nplanes,
-                (const T2*) planes, (T2*) acc);
-    else
-        es_gather_kernel<T, 17><<<grid, ES_GATHER_THREADS, 0, s>>>(*g,
-                (const Rec*) records, keys, tile_start, first_plane, nplanes,
-                (const T2*) planes, (T2*) acc);
     return (int) cudaGetLastError();
 }
 
@@ -837,7 +680,7 @@ int es_launch_tile_bounds(const EsGeom* g, const uint64_t* keys,
 int es_launch_build_records(const EsGeom* g, const void* uvw, const void* freq,
         const void* vis, const void* weight, const uint64_t* keys,
         const uint32_t* vals, int64_t num_entries, void* records,
-        es_stream_t stream)
+        const uint32_t* offsets, uint32_t* entry_pos, es_stream_t stream)
 {
     if (num_entries == 0) return 0;
     cudaStream_t s = (cudaStream_t) stream;
@@ -845,32 +688,13 @@ int es_launch_build_records(const EsGeom* g, const void* uvw, const void* freq,
         es_build_records_kernel<double><<<blocks_for(num_entries, 256), 256, 0,
                 s>>>(*g, (const double*) uvw, (const double*) freq,
                 (const double2*) vis, (const double*) weight, keys, vals,
-                num_entries, (EsRecD*) records);
+                num_entries, (EsRecD*) records, offsets, entry_pos);
     else
         es_build_records_kernel<float><<<blocks_for(num_entries, 256), 256, 0,
                 s>>>(*g, (const float*) uvw, (const float*) freq,
                 (const float2*) vis, (const float*) weight, keys, vals,
-                num_entries, (EsRecF*) records);
+                num_entries, (EsRecF*) records, offsets, entry_pos);
     return (int) cudaGetLastError();
-}
-
-int es_launch_scatter(const EsGeom* g, const void* records,
-        const uint64_t* keys, const uint32_t* tile_start, int first_plane,
-        int nplanes, void* planes, es_stream_t stream)
-{
-    cudaStream_t s = (cudaStream_t) stream;
-    const bool wide = g->support + 1 > 16;
-    if (g->is_double)
-        return wide ?
-            launch_scatter_t<double, 32>(g, records, keys, tile_start,
-                    first_plane, nplanes, planes, s) :
-            launch_scatter_t<double, 16>(g, records, keys, tile_start,
-                    first_plane, nplanes, planes, s);
-    return wide ?
-        launch_scatter_t<float, 32>(g, records, keys, tile_start, first_plane,
-                nplanes, planes, s) :
-        launch_scatter_t<float, 16>(g, records, keys, tile_start, first_plane,
-                nplanes, planes, s);
 }
 
 int es_launch_apply_screen(const EsGeom* g, const void* planes,
@@ -914,18 +738,6 @@ int es_launch_reverse_screen(const EsGeom* g, const void* dirty,
     return (int) cudaGetLastError();
 }
 
-int es_launch_gather(const EsGeom* g, const void* records,
-        const uint64_t* keys, const uint32_t* tile_start, int first_plane,
-        int nplanes, const void* planes, void* acc, es_stream_t stream)
-{
-    cudaStream_t s = (cudaStream_t) stream;
-    return g->is_double ?
-        launch_gather_t<double>(g, records, keys, tile_start, first_plane,
-                nplanes, planes, acc, s) :
-        launch_gather_t<float>(g, records, keys, tile_start, first_plane,
-                nplanes, planes, acc, s);
-}
-
 int es_launch_gather2(const EsGeom* g, const void* records, const void* units,
         uint32_t* counters, int first_plane, int nplanes, const void* planes,
         void* acc, es_stream_t stream)
@@ -951,18 +763,20 @@ int es_launch_gather2(const EsGeom* g, const void* records, const void* units,
 }
 
 int es_launch_finish_degrid(const EsGeom* g, const void* records,
-        const void* acc, int64_t num_entries, void* vis, es_stream_t stream)
+        const void* acc, const uint32_t* offsets, const uint32_t* entry_pos,
+        int64_t num_entries, void* vis, es_stream_t stream)
 {
-    if (num_entries == 0) return 0;
+    const int64_t nvis = (int64_t) g->num_rows * g->num_chan;
+    if (num_entries == 0 || nvis == 0) return 0;
     cudaStream_t s = (cudaStream_t) stream;
     if (g->is_double)
-        es_finish_degrid_kernel<double><<<blocks_for(num_entries, 256), 256, 0,
-                s>>>((const EsRecD*) records, (const double2*) acc,
-                num_entries, (double*) vis);
+        es_finish_degrid_kernel<double><<<blocks_for(nvis, 256), 256, 0,
+                s>>>((const EsRecD*) records, (const double2*) acc, offsets,
+                entry_pos, nvis, (double2*) vis);
     else
-        es_finish_degrid_kernel<float><<<blocks_for(num_entries, 256), 256, 0,
-                s>>>((const EsRecF*) records, (const float2*) acc,
-                num_entries, (float*) vis);
+        es_finish_degrid_kernel<float><<<blocks_for(nvis, 256), 256, 0,
+                s>>>((const EsRecF*) records, (const float2*) acc, offsets,
+                entry_pos, nvis, (float2*) vis);
     return (int) cudaGetLastError();
 }
 

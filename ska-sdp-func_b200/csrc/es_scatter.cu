@@ -472,22 +472,29 @@ int launch_scatter2_t(const EsGeom* g, const void* records, const void* units,
 {
     typedef typename Prec<T>::T2 T2;
     typedef typename Prec<T>::Rec Rec;
-    static int grid_size = 0;
+    /* persistent grid and shared-memory opt-in, per device (the attribute,
+     * the SM count and the occupancy all belong to the device) */
+    static int grid_sizes[ES_MAX_DEVICES];
     const size_t smem = scatter2_smem<T, NS>();
+    int dev = 0;
+    cudaError_t err = cudaGetDevice(&dev);
+    if (err != cudaSuccess) return (int) err;
+    if (dev < 0 || dev >= ES_MAX_DEVICES) return (int) cudaErrorInvalidDevice;
+    int grid_size = __atomic_load_n(&grid_sizes[dev], __ATOMIC_ACQUIRE);
     if (grid_size == 0)
     {
-        cudaError_t err = cudaFuncSetAttribute(es_scatter2_kernel<T, NS>,
+        err = cudaFuncSetAttribute(es_scatter2_kernel<T, NS>,
                 cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
         if (err != cudaSuccess) return (int) err;
-        int dev = 0, sms = 0, per_sm = 0;
-        err = cudaGetDevice(&dev);
-        if (err == cudaSuccess) err = cudaDeviceGetAttribute(&sms,
-                cudaDevAttrMultiProcessorCount, dev);
+        int sms = 0, per_sm = 0;
+        err = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount,
+                dev);
         if (err == cudaSuccess) err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(
                 &per_sm, es_scatter2_kernel<T, NS>, ES_SC_THREADS, smem);
         if (err != cudaSuccess) return (int) err;
         if (per_sm < 1) per_sm = 1;
         grid_size = sms * per_sm;
+        __atomic_store_n(&grid_sizes[dev], grid_size, __ATOMIC_RELEASE);
     }
     es_scatter2_kernel<T, NS><<<grid_size, ES_SC_THREADS, smem, s>>>(*g,
             (const Rec*) records, (const EsUnit*) units, counters, first_plane,
