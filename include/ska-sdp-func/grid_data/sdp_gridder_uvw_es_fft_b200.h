@@ -77,6 +77,12 @@ typedef struct sdp_EsCallStats
                                 * w-screen fused (ms_fft = pass 1, ms_screen =
                                 * pass 2 + screen); 0: cuFFT 2-D plans */
     int32_t reserved_;
+    /* pruned mode, timing enabled: (64 x 64 tile, plane) and (tile row,
+     * plane) pairs that held visibilities in this call -- what the scatter /
+     * gather touched and what the row pass transformed, out of
+     * planes_processed x ntile^2 and planes_processed x ntile
+     * (ntile = ceil(grid_size / 64)) */
+    int64_t occupied_tiles, occupied_tile_rows;
 } sdp_EsCallStats;
 
 /* enable != 0: record CUDA-event timings per stage (adds stream syncs at the

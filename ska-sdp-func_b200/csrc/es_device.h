@@ -109,9 +109,11 @@ int es_launch_plane_histogram(const EsGeom* g, const void* uvw,
  * with nw = (ntile + 31) / 32. Unoccupied tiles of `planes` and unoccupied
  * tile rows of the FFT intermediate are neither written nor read. */
 size_t es_occupancy_words(const EsGeom* g);
+/* totals (device, may be NULL): [0] += occupied (tile, plane) pairs,
+ * [1] += occupied (tile row, plane) pairs of this batch. */
 int es_launch_occupancy(const EsGeom* g, const uint64_t* keys,
         const uint32_t* tile_start, int first_plane, int nplanes,
-        uint32_t* occ, es_stream_t stream);
+        uint32_t* occ, unsigned long long* totals, es_stream_t stream);
 
 /* ---- load-balanced work units (es_scatter.cu) ---- */
 

@@ -75,6 +75,7 @@ struct sdp_GridderUvwEsFft
     /* load-balanced work units of the current plane batch */
     EsBuffer units, unit_counters, split_done, partials;
     EsBuffer occ;     /* plane_batch x es_occupancy_words: occupied tiles / tile rows */
+    EsBuffer occ_totals; /* 2 x u64: occupied (tile, plane) / (tile row, plane) pairs of the call */
 
     /* staging for host arrays */
     EsBuffer st_uvw, st_freq, st_vis, st_weight, st_dirty;
@@ -327,7 +328,7 @@ void sdp_gridder_uvw_es_fft_free_plan(sdp_GridderUvwEsFft* plan)
         &plan->keys_a, &plan->keys_b, &plan->vals_a, &plan->vals_b,
         &plan->records, &plan->tile_start, &plan->sort_temp, &plan->acc,
         &plan->units, &plan->unit_counters, &plan->split_done, &plan->partials,
-        &plan->occ,
+        &plan->occ, &plan->occ_totals,
         &plan->st_uvw, &plan->st_freq, &plan->st_vis, &plan->st_weight,
         &plan->st_dirty
     };
@@ -528,6 +529,8 @@ sdp_GridderUvwEsFft* sdp_gridder_uvw_es_fft_create_plan(
                         &try_status);
                 buffer_reserve(&plan->occ, (size_t) plan->plane_batch *
                         es_occupancy_words(g) * sizeof(uint32_t), &try_status);
+                buffer_reserve(&plan->occ_totals, 2 * sizeof(uint64_t),
+                        &try_status);
             }
             if (!try_status) break;
             buffer_free(&plan->planes);
@@ -585,6 +588,14 @@ void sdp_gridder_uvw_es_fft_get_stats(const sdp_GridderUvwEsFft* plan_,
             plan->stats.ms_presort = event_ms(plan, 0, 1);
             plan->stats.ms_total = event_ms(plan, 0, 3);
             stage_collect(plan, plan->stats_pending == 2);
+            uint64_t totals[2] = {0, 0};
+            if (plan->occ_totals.ptr && cudaMemcpy(totals,
+                    plan->occ_totals.ptr, sizeof(totals),
+                    cudaMemcpyDeviceToHost) == cudaSuccess)
+            {
+                plan->stats.occupied_tiles = (int64_t) totals[0];
+                plan->stats.occupied_tile_rows = (int64_t) totals[1];
+            }
         }
         else
         {
@@ -970,6 +981,9 @@ static void events_begin(sdp_GridderUvwEsFft* plan)
     plan->stats.pruned_fft = plan->pruned_fft ? 1 : 0;
     plan->stage_used = 0;
     plan->batch_used = 0;
+    if (plan->occ_totals.ptr)
+        (void) cudaMemsetAsync(plan->occ_totals.ptr, 0, 2 * sizeof(uint64_t),
+                plan->stream);
     if (plan->timing && !plan->have_events)
     {
         int ok = 1;
@@ -1111,7 +1125,8 @@ void sdp_grid_uvw_es_fft(sdp_GridderUvwEsFft* plan, const sdp_Mem* uvw,
         if (plan->pruned_fft)
             ES_CUDA(es_launch_occupancy(g, (const uint64_t*) plan->keys_b.ptr,
                     (const uint32_t*) plan->tile_start.ptr, first, nb,
-                    (uint32_t*) plan->occ.ptr, s));
+                    (uint32_t*) plan->occ.ptr,
+                    (unsigned long long*) plan->occ_totals.ptr, s));
         ES_CUDA(es_launch_work_plan(g, (const uint64_t*) plan->keys_b.ptr,
                 (const uint32_t*) plan->tile_start.ptr, first, nb, 1,
                 lim.split, lim.max_units, ES_MAX_SPLIT_ITEMS, lim.max_partials,
@@ -1235,7 +1250,8 @@ void sdp_ifft_degrid_uvw_es(sdp_GridderUvwEsFft* plan, const sdp_Mem* uvw,
             /* only the tiles the gather reads are produced */
             ES_CUDA(es_launch_occupancy(g, (const uint64_t*) plan->keys_b.ptr,
                     (const uint32_t*) plan->tile_start.ptr, first, nb,
-                    (uint32_t*) plan->occ.ptr, s));
+                    (uint32_t*) plan->occ.ptr,
+                    (unsigned long long*) plan->occ_totals.ptr, s));
             ES_CUDA(es_fft_degrid_cols(plan->pruned_fft, g,
                     plan->image_t.ptr, first, nb, plan->strip.ptr,
                     (const uint32_t*) plan->occ.ptr, s));

@@ -124,7 +124,7 @@ __global__ void __launch_bounds__(256) es_work_plan_kernel(EsGeom g,
 __global__ void __launch_bounds__(256) es_occupancy_kernel(EsGeom g,
         const uint64_t* __restrict__ keys,
         const uint32_t* __restrict__ tile_start, int first_plane, int nplanes,
-        uint32_t* __restrict__ occ)
+        uint32_t* __restrict__ occ, unsigned long long* __restrict__ totals)
 {
     const int ntiles = g.ntile * g.ntile;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -138,7 +138,15 @@ __global__ void __launch_bounds__(256) es_occupancy_kernel(EsGeom g,
     const int nw = (g.ntile + 31) >> 5;
     uint32_t* o = occ + (size_t) q * (size_t) ((g.ntile + 1) * nw);
     atomicOr(&o[tu * nw + (tv >> 5)], 1u << (tv & 31));
-    atomicOr(&o[g.ntile * nw + (tu >> 5)], 1u << (tu & 31));
+    const uint32_t row_bit = 1u << (tu & 31);
+    const uint32_t before = atomicOr(&o[g.ntile * nw + (tu >> 5)], row_bit);
+    /* call totals for the statistics: occupied (tile, plane) and
+     * (tile row, plane) pairs */
+    if (totals)
+    {
+        atomicAdd(&totals[0], 1ULL);
+        if (!(before & row_bit)) atomicAdd(&totals[1], 1ULL);
+    }
 }
 
 /* ------------------------------------------------------------- scatter */
@@ -523,7 +531,7 @@ size_t es_occupancy_words(const EsGeom* g)
 
 int es_launch_occupancy(const EsGeom* g, const uint64_t* keys,
         const uint32_t* tile_start, int first_plane, int nplanes,
-        uint32_t* occ, es_stream_t stream)
+        uint32_t* occ, unsigned long long* totals, es_stream_t stream)
 {
     cudaStream_t s = (cudaStream_t) stream;
     cudaError_t err = cudaMemsetAsync(occ, 0, (size_t) nplanes *
@@ -531,7 +539,7 @@ int es_launch_occupancy(const EsGeom* g, const uint64_t* keys,
     if (err != cudaSuccess) return (int) err;
     const int nitems = g->ntile * g->ntile * nplanes;
     es_occupancy_kernel<<<(nitems + 255) / 256, 256, 0, s>>>(*g, keys,
-            tile_start, first_plane, nplanes, occ);
+            tile_start, first_plane, nplanes, occ, totals);
     return (int) cudaGetLastError();
 }
 

@@ -68,6 +68,8 @@ class EsCallStats(ctypes.Structure):
         ("timing_enabled", ctypes.c_int32),
         ("pruned_fft", ctypes.c_int32),
         ("reserved_", ctypes.c_int32),
+        ("occupied_tiles", ctypes.c_int64),
+        ("occupied_tile_rows", ctypes.c_int64),
     ]
 
     def as_dict(self):
@@ -222,6 +224,19 @@ class GridderUvwEsFft(StructWrapper):
         """Record per-call device timings (adds a sync per call)."""
         Lib.sdp_gridder_uvw_es_fft_enable_timing(self, int(bool(enable)))
 
+    def batch_times(self, capacity=65536):
+        """(first_plane, num_planes, ms) arrays: device time of every w-plane
+        batch of the last call (timing must be enabled)."""
+        first = np.zeros(capacity, dtype=np.int32)
+        count = np.zeros(capacity, dtype=np.int32)
+        ms = np.zeros(capacity, dtype=np.float64)
+        n = Lib.sdp_gridder_uvw_es_fft_get_batch_times(
+            self, capacity,
+            first.ctypes.data_as(ctypes.POINTER(ctypes.c_int32)),
+            count.ctypes.data_as(ctypes.POINTER(ctypes.c_int32)),
+            ms.ctypes.data_as(ctypes.POINTER(ctypes.c_double)))
+        return first[:n].copy(), count[:n].copy(), ms[:n].copy()
+
     def stats(self):
         """Statistics of the last grid / degrid call as a dict."""
         out = EsCallStats()
@@ -287,6 +302,12 @@ Lib.wrap_func(
     "sdp_gridder_uvw_es_fft_enable_timing",
     restype=None,
     argtypes=[_PLAN, ctypes.c_int32],
+)
+Lib.wrap_func(
+    "sdp_gridder_uvw_es_fft_get_batch_times",
+    restype=ctypes.c_int32,
+    argtypes=[_PLAN, ctypes.c_int32, ctypes.POINTER(ctypes.c_int32),
+              ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_double)],
 )
 Lib.wrap_func(
     "sdp_gridder_uvw_es_fft_get_stats",
