@@ -45,6 +45,9 @@
 
 #define ES_FFT_COL_GROUP 16 /* degridding column pass: bundles per CTA group */
 #define ES_FFT_THREADS 512 /* upper bound of the CTA size (128 registers each) */
+#define ES_FFT_THREADS_WIDE 1024 /* variant for radices <= 16: 64 registers each,
+                                  * twice the resident warps per line (fp32 only) */
+#define ES_FFT_WIDE_MAX_RADIX 16
 #define ES_FFT_MAX_SMEM (227 * 1024 - 512) /* 512 B of static occupancy flags */
 
 /* CTA shape of one kernel family. */
@@ -383,7 +386,8 @@ template<typename T, typename T2> struct ScreenIn
 /* All passes of the lines held by this CTA; `after_first` runs once the
  * first pass is complete (all global loads done) and may end the CTA early by
  * returning false. */
-template<int SGN, bool DIT, typename T, typename T2, typename In, typename Out>
+template<int SGN, bool DIT, typename T, int MAXR, typename T2, typename In,
+        typename Out>
 __device__ __forceinline__ void fft_all_passes(T2* x, const EsFftLine& pl,
         const T2* tw, const int32_t* __restrict__ bpos, const int lshift,
         const int pitch, In& in, Out& out)
@@ -391,7 +395,7 @@ __device__ __forceinline__ void fft_all_passes(T2* x, const EsFftLine& pl,
     for (int step = 0; step < pl.num_stages; ++step)
     {
         if (step > 0) __syncthreads();
-        es_line_pass<SGN, DIT, T>(x, pl, step, tw, bpos, lshift, pitch,
+        es_line_pass<SGN, DIT, T, MAXR>(x, pl, step, tw, bpos, lshift, pitch,
                 (int) threadIdx.x, (int) blockDim.x, in, out);
     }
 }
@@ -433,8 +437,8 @@ __device__ __forceinline__ bool occ_fetch(uint8_t* s_bits,
 
 /* ------------------------------------------------------ gridding pass 1 */
 
-template<typename T>
-__global__ void __launch_bounds__(ES_FFT_THREADS, 1) es_fft_grid_rows_kernel(
+template<typename T, int MAXT>
+__global__ void __launch_bounds__(MAXT, 1) es_fft_grid_rows_kernel(
         const EsFftLine pl, const typename Cx<T>::T2* __restrict__ tw_g,
         const int32_t* __restrict__ bpos,
         const typename Cx<T>::T2* __restrict__ planes,
@@ -471,7 +475,7 @@ __global__ void __launch_bounds__(ES_FFT_THREADS, 1) es_fft_grid_rows_kernel(
     __syncthreads();
     for (int step = 0; step < pl.num_stages; ++step)
     {
-        es_line_pass<1, false, T>(x, pl, step, tw, bpos, lay.rshift,
+        es_line_pass<1, false, T, (MAXT > ES_FFT_THREADS ? ES_FFT_WIDE_MAX_RADIX : 32)>(x, pl, step, tw, bpos, lay.rshift,
                 lay.rows_pitch, (int) threadIdx.x, (int) blockDim.x, in, out);
         if (step + 1 == pl.num_stages) break;
         if (step == 0)
@@ -501,8 +505,8 @@ __global__ void __launch_bounds__(ES_FFT_THREADS, 1) es_fft_grid_rows_kernel(
  * bundle (which stays in L2 meanwhile). A pixel always receives its
  * contributions from the same thread in plane order, so the sum does not
  * depend on scheduling (bitwise reproducible). */
-template<typename T>
-__global__ void __launch_bounds__(ES_FFT_THREADS, 1)
+template<typename T, int MAXT>
+__global__ void __launch_bounds__(MAXT, 1)
 es_fft_grid_cols_screen_kernel(const EsFftLine pl,
         const typename Cx<T>::T2* __restrict__ tw_g,
         const int32_t* __restrict__ bpos, const EsGeom g,
@@ -547,7 +551,7 @@ es_fft_grid_cols_screen_kernel(const EsFftLine pl,
         for (int step = 0; step < pl.num_stages; ++step)
         {
             if (step > 0) __syncthreads();
-            es_line_pass<1, false, T>(x, pl, step, tw, bpos, lay.lshift,
+            es_line_pass<1, false, T, (MAXT > ES_FFT_THREADS ? ES_FFT_WIDE_MAX_RADIX : 32)>(x, pl, step, tw, bpos, lay.lshift,
                     lay.cols_pitch, (int) threadIdx.x, (int) blockDim.x, in,
                     out);
         }
@@ -556,8 +560,8 @@ es_fft_grid_cols_screen_kernel(const EsFftLine pl,
 
 /* ---------------------------------------------------- degridding pass 1 */
 
-template<typename T>
-__global__ void __launch_bounds__(ES_FFT_THREADS, 1) es_fft_degrid_cols_kernel(
+template<typename T, int MAXT>
+__global__ void __launch_bounds__(MAXT, 1) es_fft_degrid_cols_kernel(
         const EsFftLine pl, const typename Cx<T>::T2* __restrict__ tw_g,
         const int32_t* __restrict__ bpos, const EsGeom g,
         const T* __restrict__ image_t, const int first_plane,
@@ -605,14 +609,15 @@ __global__ void __launch_bounds__(ES_FFT_THREADS, 1) es_fft_degrid_cols_kernel(
     out.count = gsz;
     load_twiddles(tw, tw_g, pl.num_twiddles);
     __syncthreads();
-    fft_all_passes<-1, true, T>(x, pl, tw, bpos, lay.lshift, lay.cols_pitch,
-            in, out);
+    fft_all_passes<-1, true, T,
+            (MAXT > ES_FFT_THREADS ? ES_FFT_WIDE_MAX_RADIX : 32)>(x, pl, tw, bpos,
+            lay.lshift, lay.cols_pitch, in, out);
 }
 
 /* ---------------------------------------------------- degridding pass 2 */
 
-template<typename T>
-__global__ void __launch_bounds__(ES_FFT_THREADS, 1) es_fft_degrid_rows_kernel(
+template<typename T, int MAXT>
+__global__ void __launch_bounds__(MAXT, 1) es_fft_degrid_rows_kernel(
         const EsFftLine pl, const typename Cx<T>::T2* __restrict__ tw_g,
         const int32_t* __restrict__ bpos,
         const typename Cx<T>::T2* __restrict__ strip,
@@ -646,8 +651,9 @@ __global__ void __launch_bounds__(ES_FFT_THREADS, 1) es_fft_degrid_rows_kernel(
     out.count = gsz;
     load_twiddles(tw, tw_g, pl.num_twiddles);
     __syncthreads();
-    fft_all_passes<-1, true, T>(x, pl, tw, bpos, lay.rshift, lay.rows_pitch,
-            in, out);
+    fft_all_passes<-1, true, T,
+            (MAXT > ES_FFT_THREADS ? ES_FFT_WIDE_MAX_RADIX : 32)>(x, pl, tw, bpos,
+            lay.rshift, lay.rows_pitch, in, out);
 }
 
 /* ------------------------------------------------------ image transposes */
@@ -805,8 +811,16 @@ int es_fft_create(int grid_size, int image_size, int is_double, EsFft** out)
     if (env) rows_forced = sscanf(env, "%d,%d,%d,%d", &e[0], &e[1], &e[2],
             &e[3]) == 4;
     if (e[3] < 0 || e[3] > 2) e[3] = 0;
+    /* more than 512 threads: fp32 lines whose radices all fit the wide kernel
+     * variant (64 registers per thread) */
+    int max_planned = 0;
+    for (int i = 0; i < f->line.num_stages; ++i)
+        if (f->line.stage[i].radix > max_planned)
+            max_planned = f->line.stage[i].radix;
+    const int thread_cap = (!is_double && max_planned <= ES_FFT_WIDE_MAX_RADIX) ?
+            ES_FFT_THREADS_WIDE : ES_FFT_THREADS;
     for (int k = 0; k < 2; ++k)
-        if (e[k] < 0 || e[k] > ES_FFT_THREADS || (e[k] & 31)) e[k] = 0;
+        if (e[k] < 0 || e[k] > thread_cap || (e[k] & 31)) e[k] = 0;
     if (e[2] < 0 || e[2] > 2) e[2] = 0;
     /* rows of one CTA share a 64-row occupancy block and must tile the grid */
     int rshift = e[3];
@@ -877,17 +891,21 @@ int es_fft_create(int grid_size, int image_size, int is_double, EsFft** out)
     const size_t sm = ES_FFT_MAX_SMEM;
     if (!err && is_double)
     {
-        err = fft_set_smem(es_fft_grid_rows_kernel<double>, sm);
-        if (!err) err = fft_set_smem(es_fft_grid_cols_screen_kernel<double>, sm);
-        if (!err) err = fft_set_smem(es_fft_degrid_cols_kernel<double>, sm);
-        if (!err) err = fft_set_smem(es_fft_degrid_rows_kernel<double>, sm);
+        err = fft_set_smem(es_fft_grid_rows_kernel<double, ES_FFT_THREADS>, sm);
+        if (!err) err = fft_set_smem(es_fft_grid_cols_screen_kernel<double, ES_FFT_THREADS>, sm);
+        if (!err) err = fft_set_smem(es_fft_degrid_cols_kernel<double, ES_FFT_THREADS>, sm);
+        if (!err) err = fft_set_smem(es_fft_degrid_rows_kernel<double, ES_FFT_THREADS>, sm);
     }
     else if (!err)
     {
-        err = fft_set_smem(es_fft_grid_rows_kernel<float>, sm);
-        if (!err) err = fft_set_smem(es_fft_grid_cols_screen_kernel<float>, sm);
-        if (!err) err = fft_set_smem(es_fft_degrid_cols_kernel<float>, sm);
-        if (!err) err = fft_set_smem(es_fft_degrid_rows_kernel<float>, sm);
+        err = fft_set_smem(es_fft_grid_rows_kernel<float, ES_FFT_THREADS>, sm);
+        if (!err) err = fft_set_smem(es_fft_grid_rows_kernel<float, ES_FFT_THREADS_WIDE>, sm);
+        if (!err) err = fft_set_smem(es_fft_grid_cols_screen_kernel<float, ES_FFT_THREADS>, sm);
+        if (!err) err = fft_set_smem(es_fft_grid_cols_screen_kernel<float, ES_FFT_THREADS_WIDE>, sm);
+        if (!err) err = fft_set_smem(es_fft_degrid_cols_kernel<float, ES_FFT_THREADS>, sm);
+        if (!err) err = fft_set_smem(es_fft_degrid_cols_kernel<float, ES_FFT_THREADS_WIDE>, sm);
+        if (!err) err = fft_set_smem(es_fft_degrid_rows_kernel<float, ES_FFT_THREADS>, sm);
+        if (!err) err = fft_set_smem(es_fft_degrid_rows_kernel<float, ES_FFT_THREADS_WIDE>, sm);
     }
     if (err)
     {
@@ -920,12 +938,17 @@ int es_fft_grid_rows(const EsFft* f, const void* planes, int nplanes,
     const EsFftCfg& c = f->rows;
     dim3 grid((unsigned) (f->grid_size >> c.lshift), (unsigned) nplanes);
     if (f->is_double)
-        es_fft_grid_rows_kernel<double><<<grid, c.threads, c.smem_bytes,
+        es_fft_grid_rows_kernel<double, ES_FFT_THREADS><<<grid, c.threads, c.smem_bytes,
                 s>>>(f->line, (const double2*) f->d_tw, f->d_bpos,
                 (const double2*) planes, (double2*) strip, f->image_size,
                 occ, lay);
+    else if (c.threads > ES_FFT_THREADS)
+        es_fft_grid_rows_kernel<float, ES_FFT_THREADS_WIDE><<<grid, c.threads, c.smem_bytes,
+                s>>>(f->line, (const float2*) f->d_tw, f->d_bpos,
+                (const float2*) planes, (float2*) strip, f->image_size,
+                occ, lay);
     else
-        es_fft_grid_rows_kernel<float><<<grid, c.threads, c.smem_bytes,
+        es_fft_grid_rows_kernel<float, ES_FFT_THREADS><<<grid, c.threads, c.smem_bytes,
                 s>>>(f->line, (const float2*) f->d_tw, f->d_bpos,
                 (const float2*) planes, (float2*) strip, f->image_size,
                 occ, lay);
@@ -941,12 +964,17 @@ int es_fft_grid_cols_screen(const EsFft* f, const EsGeom* g, const void* strip,
     const EsFftCfg& c = f->cols;
     dim3 grid((unsigned) (f->image_size >> c.lshift));
     if (f->is_double)
-        es_fft_grid_cols_screen_kernel<double><<<grid, c.threads,
+        es_fft_grid_cols_screen_kernel<double, ES_FFT_THREADS><<<grid, c.threads,
                 c.smem_bytes, s>>>(f->line, (const double2*) f->d_tw,
                 f->d_bpos, *g, (const double2*) strip, first_plane, nplanes,
                 (double*) image_t, occ, lay);
+    else if (c.threads > ES_FFT_THREADS)
+        es_fft_grid_cols_screen_kernel<float, ES_FFT_THREADS_WIDE><<<grid, c.threads,
+                c.smem_bytes, s>>>(f->line, (const float2*) f->d_tw,
+                f->d_bpos, *g, (const float2*) strip, first_plane, nplanes,
+                (float*) image_t, occ, lay);
     else
-        es_fft_grid_cols_screen_kernel<float><<<grid, c.threads,
+        es_fft_grid_cols_screen_kernel<float, ES_FFT_THREADS><<<grid, c.threads,
                 c.smem_bytes, s>>>(f->line, (const float2*) f->d_tw,
                 f->d_bpos, *g, (const float2*) strip, first_plane, nplanes,
                 (float*) image_t, occ, lay);
@@ -964,12 +992,17 @@ int es_fft_degrid_cols(const EsFft* f, const EsGeom* g, const void* image_t,
     const int groups = (nbundles + ES_FFT_COL_GROUP - 1) / ES_FFT_COL_GROUP;
     dim3 grid((unsigned) (groups * ES_FFT_COL_GROUP * nplanes));
     if (f->is_double)
-        es_fft_degrid_cols_kernel<double><<<grid, c.threads, c.smem_bytes,
+        es_fft_degrid_cols_kernel<double, ES_FFT_THREADS><<<grid, c.threads, c.smem_bytes,
                 s>>>(f->line, (const double2*) f->d_tw, f->d_bpos, *g,
                 (const double*) image_t, first_plane, nplanes,
                 (double2*) strip, occ, lay);
+    else if (c.threads > ES_FFT_THREADS)
+        es_fft_degrid_cols_kernel<float, ES_FFT_THREADS_WIDE><<<grid, c.threads, c.smem_bytes,
+                s>>>(f->line, (const float2*) f->d_tw, f->d_bpos, *g,
+                (const float*) image_t, first_plane, nplanes,
+                (float2*) strip, occ, lay);
     else
-        es_fft_degrid_cols_kernel<float><<<grid, c.threads, c.smem_bytes,
+        es_fft_degrid_cols_kernel<float, ES_FFT_THREADS><<<grid, c.threads, c.smem_bytes,
                 s>>>(f->line, (const float2*) f->d_tw, f->d_bpos, *g,
                 (const float*) image_t, first_plane, nplanes,
                 (float2*) strip, occ, lay);
@@ -984,12 +1017,17 @@ int es_fft_degrid_rows(const EsFft* f, const void* strip, int nplanes,
     const EsFftCfg& c = f->rows;
     dim3 grid((unsigned) (f->grid_size >> c.lshift), (unsigned) nplanes);
     if (f->is_double)
-        es_fft_degrid_rows_kernel<double><<<grid, c.threads, c.smem_bytes,
+        es_fft_degrid_rows_kernel<double, ES_FFT_THREADS><<<grid, c.threads, c.smem_bytes,
                 s>>>(f->line, (const double2*) f->d_tw, f->d_bpos,
                 (const double2*) strip, (double2*) planes, f->image_size,
                 occ, lay);
+    else if (c.threads > ES_FFT_THREADS)
+        es_fft_degrid_rows_kernel<float, ES_FFT_THREADS_WIDE><<<grid, c.threads, c.smem_bytes,
+                s>>>(f->line, (const float2*) f->d_tw, f->d_bpos,
+                (const float2*) strip, (float2*) planes, f->image_size,
+                occ, lay);
     else
-        es_fft_degrid_rows_kernel<float><<<grid, c.threads, c.smem_bytes,
+        es_fft_degrid_rows_kernel<float, ES_FFT_THREADS><<<grid, c.threads, c.smem_bytes,
                 s>>>(f->line, (const float2*) f->d_tw, f->d_bpos,
                 (const float2*) strip, (float2*) planes, f->image_size,
                 occ, lay);

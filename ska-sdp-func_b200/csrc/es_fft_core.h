@@ -491,14 +491,15 @@ ES_HD void es_line_pass_body(T2* x, const EsFftLine& pl, const int stage,
  * never planned (es_fft_line_plan): they are not instantiated. */
 #define ES_FFT_MAX_RADIX_DOUBLE 16
 
-template<int R, int SGN, bool DIT, typename T, typename T2, typename In,
-        typename Out>
+template<int R, int SGN, bool DIT, int MAXR, typename T, typename T2,
+        typename In, typename Out>
 ES_HD void es_line_pass_r(T2* x, const EsFftLine& pl, const int stage,
         const bool from_in, const bool to_out, const T2* tw,
         const int32_t* bpos, const int lshift, const int pitch, const int tid,
         const int nthreads, In& in, Out& out)
 {
-    if constexpr (sizeof(T) == 4 || R <= ES_FFT_MAX_RADIX_DOUBLE)
+    if constexpr ((sizeof(T) == 4 || R <= ES_FFT_MAX_RADIX_DOUBLE) &&
+            R <= MAXR)
         es_line_pass_body<R, SGN, DIT, T>(x, pl, stage, from_in, to_out, tw,
                 bpos, lshift, pitch, tid, nthreads, in, out);
 }
@@ -513,14 +514,17 @@ ES_HD void es_line_pass_r(T2* x, const EsFftLine& pl, const int stage,
     ES_FFT_CASE(24) ES_FFT_CASE(28) ES_FFT_CASE(32)
 #endif
 
-template<int SGN, bool DIT, typename T, typename T2, typename In, typename Out>
+/* MAXR: largest radix instantiated (kernel variants with more threads and
+ * fewer registers per thread carry only the small butterflies). */
+template<int SGN, bool DIT, typename T, int MAXR = 32, typename T2, typename In,
+        typename Out>
 ES_HD void es_line_pass(T2* x, const EsFftLine& pl, const int step,
         const T2* tw, const int32_t* bpos, const int lshift, const int pitch,
         const int tid, const int nthreads, In& in, Out& out)
 {
     const int stage = DIT ? pl.num_stages - 1 - step : step;
     const bool from_in = (step == 0), to_out = (step == pl.num_stages - 1);
-#define ES_FFT_CASE(R) case R: es_line_pass_r<R, SGN, DIT, T>(x, pl, stage, \
+#define ES_FFT_CASE(R) case R: es_line_pass_r<R, SGN, DIT, MAXR, T>(x, pl, stage, \
         from_in, to_out, tw, bpos, lshift, pitch, tid, nthreads, in, out); break;
     switch (pl.stage[stage].radix)
     {

@@ -256,7 +256,8 @@ class ShardedGridderUvwEsFft:
             self._collective(dist.all_reduce, as_real, op=dist.ReduceOp.SUM)
         if host_vis and (not reduce_to_root or self.rank == root):
             torch.from_numpy(vis).copy_(d_vis)
-        if host_image:
+        if host_image and self.rank == root:
+            # host arrays: only root's image is the caller's model image
             torch.from_numpy(dirty_image).copy_(d_img)
         self._last = "degrid"
 

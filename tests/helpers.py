@@ -75,3 +75,57 @@ def check_parity(case, eps, wstack, do_grid=True, do_degrid=True):
         out["image"] = rel_max(img, o_img)
         assert out["degrid"] <= tol and out["image"] <= tol, out
     return out
+
+
+def check_parity_planes(case, eps, count, do_grid=True, do_degrid=True,
+                        image_size=None, wstack=True):
+    """Parity on a block of `count` w-planes from the middle of the lattice
+    (all planes if count is None), all visibilities of the case, at the
+    case's real grid / image size: product restricted with set_plane_range
+    against the oracle restricted to the same planes. The oracle's cost is
+    one G x G fp64 FFT per plane, which is what bounds `count` at the grid
+    sizes bench.py times (G = 6160 ... 24640). Returns (errors, plan info)."""
+    n = image_size or case["image"].shape[0]
+    real = case["uvw"].dtype
+    tol = TOL[np.dtype(real)]
+    dirty = np.zeros((n, n), dtype=real)
+    gridder = GridderUvwEsFft(case["uvw"], case["freq_hz"], case["vis"],
+                              case["weight"], dirty, case["pixel_size"],
+                              case["pixel_size"], eps, wstack)
+    info = gridder.info()
+    planes = info["num_total_w_grids"]
+    o = eo.OracleGridder(case["uvw"], case["freq_hz"], case["vis"],
+                         case["weight"], dirty, case["pixel_size"],
+                         case["pixel_size"], eps, wstack)
+    assert o.plan["grid_size"] == info["grid_size"]
+    assert o.plan["num_total_w_grids"] == planes
+    if count is None or count >= planes:
+        lo, hi = 0, planes
+    else:
+        lo = planes // 2 - count // 2
+        hi = lo + count
+    gridder.set_plane_range(lo, hi, apply_correction=True)
+    out = {}
+    if do_grid:
+        gridder.grid_uvw_es_fft(case["uvw"], case["freq_hz"], case["vis"],
+                                case["weight"], dirty)
+        want, _ = o.grid_uvw_es_fft(case["uvw"], case["freq_hz"], case["vis"],
+                                    case["weight"], planes=(lo, hi))
+        out["grid"] = rel_max(dirty, want)
+        assert np.max(np.abs(want)) > 0
+        assert out["grid"] <= tol, (out, info)
+    if do_degrid:
+        image = case.get("image")
+        if image is None or image.shape[0] != n:
+            image = np.random.default_rng(3).uniform(-0.5, 0.5, (n, n)).astype(real)
+        img = image.copy()
+        vis = np.zeros_like(case["vis"])
+        gridder.ifft_grid_uvw_es(case["uvw"], case["freq_hz"], vis,
+                                 case["weight"], img)
+        want, want_img, _ = o.ifft_grid_uvw_es(case["uvw"], case["freq_hz"],
+                                               image, planes=(lo, hi))
+        out["degrid"] = rel_max(vis, want)
+        out["image"] = rel_max(img, want_img)
+        assert np.max(np.abs(want)) > 0
+        assert out["degrid"] <= tol and out["image"] <= tol, (out, info)
+    return out, info

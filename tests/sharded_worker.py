@@ -162,7 +162,9 @@ def main():
     result["model_corrected"] = np.asarray(
         model.cpu() if torch.is_tensor(model) else model).copy()
     # every rank must hold the same prediction and the same corrected image
-    for key in ("vis", "model_corrected", "dirty"):
+    # (host arrays: only root's model image is written back)
+    same = ("vis", "dirty") if mode == "oracle" else ("vis", "model_corrected", "dirty")
+    for key in same:
         t = torch.from_numpy(np.ascontiguousarray(result[key]))
         t = torch.view_as_real(t) if t.is_complex() else t
         lo, hi = t.clone(), t.clone()

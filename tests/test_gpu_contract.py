@@ -1,0 +1,223 @@
+"""Contract cases of the CUDA path beyond plain numpy-in / numpy-out parity:
+device-resident arrays (the reference's actual contract: SDP_MEM_GPU arrays,
+work enqueued on the legacy default stream, no synchronisation before return,
+SURVEY.md 8b), plans of different sizes alive together, the cuFFT fallback
+path, bitwise reproducibility of both directions, the unmodified reference
+Python package driving this library, and the three-way comparison with the
+reference's own CUDA build (baseline/_ref)."""
+import json
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from tests import synth
+from ska_sdp_func.grid_data import GridderUvwEsFft
+from tests.helpers import (TOL, check_parity, oracle_degrid, oracle_grid,
+                           product_degrid, product_grid, rel_max)
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF = os.path.join(ROOT, "baseline", "_ref")
+
+
+@pytest.mark.parametrize("single", [True, False])
+def test_device_resident_arrays_back_to_back(single):
+    """torch CUDA tensors (SDP_MEM_GPU): grid twice and degrid twice in a row
+    with no host synchronisation between the calls or before reading the
+    results on the same (legacy default) stream; results equal the oracle."""
+    import torch
+    c = synth.reference_test_case(256, num_vis=400, num_chan=8, single=single)
+    tol = TOL[np.dtype(c["uvw"].dtype)]
+    dev = torch.device("cuda", 0)
+    t = {k: torch.from_numpy(c[k]).to(dev)
+         for k in ("uvw", "freq_hz", "vis", "weight", "image")}
+    img_a = torch.zeros_like(t["image"])
+    img_b = torch.zeros_like(t["image"])
+    g = GridderUvwEsFft(t["uvw"], t["freq_hz"], t["vis"], t["weight"], img_a,
+                        c["pixel_size"], c["pixel_size"], 1e-6, True)
+    g.grid_uvw_es_fft(t["uvw"], t["freq_hz"], t["vis"], t["weight"], img_a)
+    g.grid_uvw_es_fft(t["uvw"], t["freq_hz"], t["vis"], t["weight"], img_b)
+    model_a, model_b = t["image"].clone(), t["image"].clone()
+    vis_a, vis_b = torch.zeros_like(t["vis"]), torch.zeros_like(t["vis"])
+    g.ifft_grid_uvw_es(t["uvw"], t["freq_hz"], vis_a, t["weight"], model_a)
+    g.ifft_grid_uvw_es(t["uvw"], t["freq_hz"], vis_b, t["weight"], model_b)
+    # stream-ordered consumers: device-side arithmetic queued right behind
+    diff_img = (img_a - img_b).abs().max()
+    diff_vis = (vis_a - vis_b).abs().max()
+    want = oracle_grid(c, 1e-6, True)
+    want_vis, want_img = oracle_degrid(c, 1e-6, True)
+    assert float(diff_img) == 0.0 and float(diff_vis) == 0.0
+    assert rel_max(img_b.cpu().numpy(), want) <= tol
+    assert rel_max(vis_b.cpu().numpy(), want_vis) <= tol
+    assert rel_max(model_b.cpu().numpy(), want_img) <= tol
+
+
+def test_two_plans_of_different_sizes_alive_together():
+    """The dynamic shared-memory opt-in belongs to the kernel and the device,
+    not to a plan: create a large plan, then a small one of the
+    same precision, then run the large one."""
+    big = synth.uniform_box(200, 64, 2048, single=True)
+    small = synth.reference_test_case(128, num_vis=50, num_chan=2, single=True)
+    d_big0, g_big = product_grid(big, 1e-5, True)
+    d_small, g_small = product_grid(small, 1e-5, True)
+    d_big1, _ = product_grid(big, 1e-5, True, g_big)
+    v_big, _, _ = product_degrid(big, 1e-5, True, g_big)
+    assert np.array_equal(d_big0, d_big1)
+    assert rel_max(d_small, oracle_grid(small, 1e-5, True)) <= 1e-5
+    assert rel_max(d_big1, oracle_grid(big, 1e-5, True)) <= 1e-5
+    assert rel_max(v_big, oracle_degrid(big, 1e-5, True)[0]) <= 1e-5
+    del g_small
+
+
+@pytest.mark.parametrize("single", [True, False])
+def test_cufft_fallback_path(monkeypatch, single):
+    """SKA_SDP_FUNC_ES_USE_CUFFT=1: batched cuFFT 2-D plans + the separate
+    w-screen / zero-padding kernels (the path sizes without a line-FFT plan
+    take), against the oracle."""
+    monkeypatch.setenv("SKA_SDP_FUNC_ES_USE_CUFFT", "1")
+    c = synth.reference_test_case(256, num_vis=300, num_chan=6, single=single)
+    out = check_parity(c, 1e-5 if single else 1e-9, True)
+    c2 = synth.reference_test_case(128, num_vis=100, num_chan=3, single=single)
+    check_parity(c2, 1e-5 if single else 1e-9, False)
+    print(out)
+
+
+def test_cufft_fallback_is_what_ran(monkeypatch):
+    monkeypatch.setenv("SKA_SDP_FUNC_ES_USE_CUFFT", "1")
+    c = synth.reference_test_case(128, num_vis=100, num_chan=3)
+    _, g = product_grid(c, 1e-6, True)
+    st = g.stats()
+    assert st["pruned_fft"] == 0 and st["fft_execs"] > 0
+    monkeypatch.delenv("SKA_SDP_FUNC_ES_USE_CUFFT")
+    _, g2 = product_grid(c, 1e-6, True)
+    st2 = g2.stats()
+    assert st2["pruned_fft"] == 1 and st2["fft_execs"] == 0
+
+
+def test_odd_image_size_takes_the_fallback():
+    """An odd image size has no pruned line-FFT plan (es_fft_create): the
+    library falls back to cuFFT by itself; reference semantics for odd N
+    (kernels.cu:444-515 mirror loop) against the oracle."""
+    c = synth.reference_test_case(255, num_vis=200, num_chan=4)
+    check_parity(c, 1e-6, True)
+    _, g = product_grid(c, 1e-6, True)
+    assert g.stats()["pruned_fft"] == 0
+
+
+@pytest.mark.parametrize("single", [True, False])
+def test_both_directions_bitwise_reproducible(single):
+    """No floating-point atomics whose order depends on scheduling: gridding
+    sums a pixel's contributions in plane order from one thread, degridding
+    sums a visibility's (at most 4) tile partials in entry order."""
+    c = synth.ska_low_snapshot(48, 16, 512, single=single, r_max=2e3)
+    d0, g = product_grid(c, 1e-5, True)
+    v0, _, _ = product_degrid(c, 1e-5, True, g)
+    for _ in range(3):
+        d1, _ = product_grid(c, 1e-5, True, g)
+        v1, _, _ = product_degrid(c, 1e-5, True, g)
+        assert np.array_equal(d0, d1)
+        assert np.array_equal(v0, v1)
+
+
+REF_PY_DRIVER = r"""
+import sys, numpy as np
+sys.path.insert(0, sys.argv[1])            # the UNMODIFIED reference package
+import ska_sdp_func
+from ska_sdp_func.utility import Lib
+from ska_sdp_func.grid_data import GridderUvwEsFft
+assert ska_sdp_func.__file__.startswith(sys.argv[1]), ska_sdp_func.__file__
+z = np.load(sys.argv[2])
+uvw, freq, vis, wgt, image = (z[k] for k in ("uvw", "freq_hz", "vis", "weight", "image"))
+pix = float(z["pixel_size"])
+dirty = np.zeros_like(image)
+g = GridderUvwEsFft(uvw, freq, vis, wgt, dirty, pix, pix, 1e-6, True)
+g.grid_uvw_es_fft(uvw, freq, vis, wgt, dirty)
+pred = np.zeros_like(vis)
+img = image.copy()
+g.ifft_grid_uvw_es(uvw, freq, pred, wgt, img)
+np.savez(sys.argv[3], dirty=dirty, pred=pred, img=img, lib=np.array(Lib.find_lib()))
+"""
+
+
+def _reference_package_dir():
+    for d in (REF, "/root/reference/src"):
+        if os.path.exists(os.path.join(d, "ska_sdp_func", "grid_data",
+                                       "gridder_uvw_es_fft.py")):
+            return d
+    return None
+
+
+def test_unmodified_reference_python_package_drives_this_library(tmp_path):
+    """The reference's own ska_sdp_func package (baseline/_ref, or
+    /root/reference/src where it exists), pointed at THIS libska_sdp_func.so
+    with SKA_SDP_FUNC_LIB_DIR, on numpy arrays, grid + degrid, in its own
+    process: the drop-in claim of INTEGRATION.md section 2."""
+    pkg = _reference_package_dir()
+    if pkg is None:
+        pytest.skip("no copy of the reference Python package on this box")
+    from ska_sdp_func.utility import Lib
+    lib_dir = os.path.dirname(Lib.find_lib())
+    c = synth.reference_test_case(256, num_vis=300, num_chan=6)
+    inp, outp = str(tmp_path / "in.npz"), str(tmp_path / "out.npz")
+    np.savez(inp, **{k: c[k] for k in ("uvw", "freq_hz", "vis", "weight", "image")},
+             pixel_size=c["pixel_size"])
+    env = {k: v for k, v in os.environ.items() if k != "PYTHONPATH"}
+    env["SKA_SDP_FUNC_LIB_DIR"] = lib_dir
+    r = subprocess.run([sys.executable, "-c", REF_PY_DRIVER, pkg, inp, outp],
+                       env=env, capture_output=True, text=True, cwd=str(tmp_path),
+                       timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    z = np.load(outp)
+    assert os.path.realpath(str(z["lib"])).startswith(os.path.realpath(lib_dir))
+    assert rel_max(z["dirty"], oracle_grid(c, 1e-6, True)) <= 1e-10
+    want_vis, want_img = oracle_degrid(c, 1e-6, True)
+    assert rel_max(z["pred"], want_vis) <= 1e-10
+    assert rel_max(z["img"], want_img) <= 1e-10
+
+
+@pytest.mark.parametrize("single", [False, True])
+def test_three_way_with_the_reference_cuda_build(single, tmp_path):
+    """SURVEY.md 7.5 #1 with the real GPU build in it: the unmodified
+    reference library (baseline/_ref, sm_100 cubins) through its own Python
+    class on the same C1 inputs, in its own process. Reports new-vs-oracle64,
+    ref-gpu-vs-oracle64 and new-vs-ref-gpu; fp64: all <= 1e-10; fp32: ours
+    must meet 1e-5 against the oracle, the reference's fp32 arithmetic is
+    reported (its coordinates are fp32)."""
+    if not os.path.exists(os.path.join(REF, "libska_sdp_func.so")):
+        pytest.skip("baseline/_ref not installed (baseline/build_ref_gpu.sh)")
+    c = synth.reference_test_case(256, single=single)
+    outs = {}
+    for direction in ("grid", "degrid"):
+        path = str(tmp_path / f"ref_{direction}.npz")
+        r = subprocess.run(
+            [sys.executable, os.path.join(ROOT, "baseline", "ref_gpu.py"),
+             "--workload", "C1", "--single", str(int(single)), "--direction",
+             direction, "--steps", "1", "--out", path],
+            capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, r.stdout + r.stderr
+        res = json.loads([ln for ln in r.stdout.splitlines()
+                          if ln.startswith("{")][-1])
+        assert res["available"], res
+        outs[direction] = np.load(path)
+    ref_dirty, ref_vis = outs["grid"]["dirty"], outs["degrid"]["vis"]
+    dirty, g = product_grid(c, 1e-5, True)
+    vis, _, _ = product_degrid(c, 1e-5, True, g)
+    o_dirty = oracle_grid(c, 1e-5, True)
+    o_vis, _ = oracle_degrid(c, 1e-5, True)
+    table = {
+        "new-vs-oracle64": (rel_max(dirty, o_dirty), rel_max(vis, o_vis)),
+        "refgpu-vs-oracle64": (rel_max(ref_dirty, o_dirty), rel_max(ref_vis, o_vis)),
+        "new-vs-refgpu": (rel_max(dirty, ref_dirty), rel_max(vis, ref_vis)),
+    }
+    print("three-way", "fp32" if single else "fp64", table)
+    tol = TOL[np.dtype(c["uvw"].dtype)]
+    assert max(table["new-vs-oracle64"]) <= tol
+    if not single:
+        assert max(table["refgpu-vs-oracle64"]) <= tol
+        assert max(table["new-vs-refgpu"]) <= tol
+    else:
+        assert max(table["refgpu-vs-oracle64"]) <= 1e-3   # fp32 coordinates
