@@ -67,6 +67,11 @@ struct EsFft
     EsFftCfg rows;    /* one line per CTA */
     EsFftCfg cols;    /* 1 << lshift adjacent columns per CTA */
     int64_t plane_elems; /* elements of the intermediate per plane */
+    /* row passes: persistent CTAs over the occupied tile rows of a batch */
+    uint32_t* d_row_list; /* (plane << 16 | tile row), ascending */
+    uint32_t* d_row_work; /* [0] work items of the batch, [1] next item */
+    int32_t row_list_cap; /* entries */
+    int32_t rows_grid;    /* resident CTAs of the row kernels on this device */
 };
 
 namespace {
@@ -435,6 +440,82 @@ __device__ __forceinline__ bool occ_fetch(uint8_t* s_bits,
     return __syncthreads_or((int) any) != 0;
 }
 
+/* ----------------------------------------------- occupied tile-row list */
+
+/* One CTA: the occupied (plane, tile row) pairs of the batch in ascending
+ * order -> list, work[0] = pairs x row bundles per tile row, work[1] = 0.
+ * The row kernels then run as persistent CTAs over exactly the rows that
+ * hold data: on sparse coverage (SKA-Low: a quarter of the tile rows) most
+ * CTAs of a (rows x planes) launch would only find out that they have
+ * nothing to do, one shared-memory-filling CTA per SM at a time. */
+__global__ void __launch_bounds__(1024) es_fft_row_list_kernel(
+        const uint32_t* __restrict__ occ, const EsFftLayout lay,
+        const int nplanes, uint32_t* __restrict__ list,
+        uint32_t* __restrict__ work)
+{
+    __shared__ uint32_t s_base, s_warp[32];
+    const int total = nplanes * lay.ntile;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) s_base = 0u;
+    __syncthreads();
+    for (int i0 = 0; i0 < total; i0 += (int) blockDim.x)
+    {
+        const int i = i0 + (int) threadIdx.x;
+        bool on = false;
+        int q = 0, tu = 0;
+        if (i < total)
+        {
+            q = i / lay.ntile;
+            tu = i - q * lay.ntile;
+            const uint32_t* o = occ + (size_t) q *
+                    (size_t) ((lay.ntile + 1) * lay.occ_nw) +
+                    lay.ntile * lay.occ_nw;
+            on = (o[tu >> 5] >> (tu & 31)) & 1u;
+        }
+        const uint32_t m = __ballot_sync(0xffffffffu, on);
+        if (lane == 0) s_warp[warp] = (uint32_t) __popc(m);
+        __syncthreads();
+        uint32_t before = s_base;
+        for (int w = 0; w < warp; ++w) before += s_warp[w];
+        if (on)
+            list[before + (uint32_t) __popc(m & ((1u << lane) - 1u))] =
+                    ((uint32_t) q << 16) | (uint32_t) tu;
+        __syncthreads();
+        if (threadIdx.x == 0)
+        {
+            uint32_t sum = 0u;
+            for (int w = 0; w < (int) (blockDim.x >> 5); ++w) sum += s_warp[w];
+            s_base += sum;
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0)
+    {
+        work[0] = s_base * (uint32_t) (ES_TILE >> lay.rshift);
+        work[1] = 0u;
+    }
+}
+
+/* Next work item of a persistent row CTA (contains barriers: the previous
+ * item's shared-memory traffic is complete when it returns). Item ->
+ * first row u of the bundle and plane q; false when the list is exhausted. */
+__device__ __forceinline__ bool row_item(uint32_t* s_item,
+        const uint32_t* __restrict__ list, uint32_t* __restrict__ work,
+        const EsFftLayout& lay, int& q, int& u)
+{
+    __syncthreads();
+    if (threadIdx.x == 0) *s_item = atomicAdd(&work[1], 1u);
+    __syncthreads();
+    const uint32_t item = *s_item;
+    if (item >= work[0]) return false;
+    const int per_shift = 6 - lay.rshift; /* row bundles per tile row */
+    const uint32_t e = list[item >> per_shift];
+    q = (int) (e >> 16);
+    u = (int) ((e & 0xffffu) << 6) +
+            (int) ((item & ((1u << per_shift) - 1u)) << lay.rshift);
+    return true;
+}
+
 /* ------------------------------------------------------ gridding pass 1 */
 
 template<typename T, int MAXT>
@@ -443,57 +524,65 @@ __global__ void __launch_bounds__(MAXT, 1) es_fft_grid_rows_kernel(
         const int32_t* __restrict__ bpos,
         const typename Cx<T>::T2* __restrict__ planes,
         typename Cx<T>::T2* __restrict__ strip, const int image_size,
-        const uint32_t* __restrict__ occ, const EsFftLayout lay)
+        const uint32_t* __restrict__ occ, const EsFftLayout lay,
+        const uint32_t* __restrict__ row_list, uint32_t* __restrict__ row_work)
 {
     typedef typename Cx<T>::T2 T2;
     extern __shared__ __align__(16) unsigned char es_fft_smem[];
     __shared__ uint8_t s_bits[ES_FFT_OCC_BYTES];
+    __shared__ uint32_t s_item;
     T2* x = (T2*) es_fft_smem;
     const T2* tw = lay.rows_twg ? tw_g :
             x + ((size_t) lay.rows_pitch << lay.rshift);
     const int gsz = pl.n, n = image_size;
-    const int u = blockIdx.x << lay.rshift; /* first row of the bundle */
-    /* nothing was gridded onto this tile row: the column pass reads it as
-     * zeros without it being stored */
-    if (!occ_fetch(s_bits, occ_plane(occ, lay, blockIdx.y) +
-            (u >> 6) * lay.occ_nw, lay.occ_nw)) return;
-    LinearIn<T2, false, true, true> in;
-    in.bits = s_bits;
-    in.base = planes + ((size_t) blockIdx.y * gsz + u) * gsz;
-    in.estride = 1;
-    in.lstride = gsz;
-    in.k0 = 0;
-    in.count = gsz;
-    in.any = 0u;
-    LinearOut<T2, true> out;
-    out.base = strip + (size_t) blockIdx.y * lay.plane_elems + (size_t) u * n;
-    out.estride = 1;
-    out.lstride = n;
-    out.k0 = gsz / 2 - n / 2;
-    out.count = n;
     load_twiddles(tw, tw_g, pl.num_twiddles);
-    __syncthreads();
-    for (int step = 0; step < pl.num_stages; ++step)
+    /* persistent CTA: row bundles of tile rows that hold data, nothing else
+     * (rows of the other tile rows are read as zeros by the column pass
+     * without ever being stored) */
+    int q, u;
+    while (row_item(&s_item, row_list, row_work, lay, q, u))
     {
-        es_line_pass<1, false, T, (MAXT > ES_FFT_THREADS ? ES_FFT_WIDE_MAX_RADIX : 32)>(x, pl, step, tw, bpos, lay.rshift,
-                lay.rows_pitch, (int) threadIdx.x, (int) blockDim.x, in, out);
-        if (step + 1 == pl.num_stages) break;
-        if (step == 0)
+        if (u >= gsz) continue; /* the last tile row may be partial */
+        occ_fetch(s_bits, occ_plane(occ, lay, q) + (u >> 6) * lay.occ_nw,
+                lay.occ_nw);
+        LinearIn<T2, false, true, true> in;
+        in.bits = s_bits;
+        in.base = planes + ((size_t) q * gsz + u) * gsz;
+        in.estride = 1;
+        in.lstride = gsz;
+        in.k0 = 0;
+        in.count = gsz;
+        in.any = 0u;
+        LinearOut<T2, true> out;
+        out.base = strip + (size_t) q * lay.plane_elems + (size_t) u * n;
+        out.estride = 1;
+        out.lstride = n;
+        out.k0 = gsz / 2 - n / 2;
+        out.count = n;
+        for (int step = 0; step < pl.num_stages; ++step)
         {
-            /* rows nothing was gridded onto transform to zeros */
-            if (!__syncthreads_or((int) (in.any != 0u)))
+            es_line_pass<1, false, T,
+                    (MAXT > ES_FFT_THREADS ? ES_FFT_WIDE_MAX_RADIX : 32)>(x, pl,
+                    step, tw, bpos, lay.rshift, lay.rows_pitch,
+                    (int) threadIdx.x, (int) blockDim.x, in, out);
+            if (step + 1 == pl.num_stages) break;
+            if (step == 0)
             {
-                T2 zero;
-                zero.x = 0; zero.y = 0;
-                for (int i = threadIdx.x; i < (n << lay.rshift);
-                        i += blockDim.x)
-                    out.base[i] = zero; /* the rows of a bundle are adjacent */
-                return;
+                /* rows nothing was gridded onto transform to zeros */
+                if (!__syncthreads_or((int) (in.any != 0u)))
+                {
+                    T2 zero;
+                    zero.x = 0; zero.y = 0;
+                    for (int i = threadIdx.x; i < (n << lay.rshift);
+                            i += blockDim.x)
+                        out.base[i] = zero; /* the rows of a bundle are adjacent */
+                    break;
+                }
             }
-        }
-        else
-        {
-            __syncthreads();
+            else
+            {
+                __syncthreads();
+            }
         }
     }
 }
@@ -622,38 +711,44 @@ __global__ void __launch_bounds__(MAXT, 1) es_fft_degrid_rows_kernel(
         const int32_t* __restrict__ bpos,
         const typename Cx<T>::T2* __restrict__ strip,
         typename Cx<T>::T2* __restrict__ planes, const int image_size,
-        const uint32_t* __restrict__ occ, const EsFftLayout lay)
+        const uint32_t* __restrict__ occ, const EsFftLayout lay,
+        const uint32_t* __restrict__ row_list, uint32_t* __restrict__ row_work)
 {
     typedef typename Cx<T>::T2 T2;
     extern __shared__ __align__(16) unsigned char es_fft_smem[];
     __shared__ uint8_t s_bits[ES_FFT_OCC_BYTES];
+    __shared__ uint32_t s_item;
     T2* x = (T2*) es_fft_smem;
     const T2* tw = lay.rows_twg ? tw_g :
             x + ((size_t) lay.rows_pitch << lay.rshift);
     const int gsz = pl.n, n = image_size;
-    const int u = blockIdx.x << lay.rshift;
-    /* only the tiles the gather reads are stored */
-    if (!occ_fetch(s_bits, occ_plane(occ, lay, blockIdx.y) +
-            (u >> 6) * lay.occ_nw, lay.occ_nw)) return;
-    LinearIn<T2, true, false> in;
-    in.base = strip + (size_t) blockIdx.y * lay.plane_elems + (size_t) u * n;
-    in.estride = 1;
-    in.lstride = n;
-    in.k0 = gsz / 2 - n / 2;
-    in.count = n;
-    in.any = 0u;
-    LinearOut<T2, false, true> out;
-    out.bits = s_bits;
-    out.base = planes + ((size_t) blockIdx.y * gsz + u) * gsz;
-    out.estride = 1;
-    out.lstride = gsz;
-    out.k0 = 0;
-    out.count = gsz;
     load_twiddles(tw, tw_g, pl.num_twiddles);
-    __syncthreads();
-    fft_all_passes<-1, true, T,
-            (MAXT > ES_FFT_THREADS ? ES_FFT_WIDE_MAX_RADIX : 32)>(x, pl, tw, bpos,
-            lay.rshift, lay.rows_pitch, in, out);
+    /* persistent CTA over the tile rows the gather reads; only their
+     * occupied tiles are stored */
+    int q, u;
+    while (row_item(&s_item, row_list, row_work, lay, q, u))
+    {
+        if (u >= gsz) continue;
+        occ_fetch(s_bits, occ_plane(occ, lay, q) + (u >> 6) * lay.occ_nw,
+                lay.occ_nw);
+        LinearIn<T2, true, false> in;
+        in.base = strip + (size_t) q * lay.plane_elems + (size_t) u * n;
+        in.estride = 1;
+        in.lstride = n;
+        in.k0 = gsz / 2 - n / 2;
+        in.count = n;
+        in.any = 0u;
+        LinearOut<T2, false, true> out;
+        out.bits = s_bits;
+        out.base = planes + ((size_t) q * gsz + u) * gsz;
+        out.estride = 1;
+        out.lstride = gsz;
+        out.k0 = 0;
+        out.count = gsz;
+        fft_all_passes<-1, true, T,
+                (MAXT > ES_FFT_THREADS ? ES_FFT_WIDE_MAX_RADIX : 32)>(x, pl, tw,
+                bpos, lay.rshift, lay.rows_pitch, in, out);
+    }
 }
 
 /* ------------------------------------------------------ image transposes */
@@ -907,6 +1002,30 @@ int es_fft_create(int grid_size, int image_size, int is_double, EsFft** out)
         if (!err) err = fft_set_smem(es_fft_degrid_rows_kernel<float, ES_FFT_THREADS>, sm);
         if (!err) err = fft_set_smem(es_fft_degrid_rows_kernel<float, ES_FFT_THREADS_WIDE>, sm);
     }
+    if (!err)
+    {
+        /* persistent row kernels: as many CTAs as the device holds at once */
+        int dev = 0, sms = 0, per_sm = 0;
+        err = (int) cudaGetDevice(&dev);
+        if (!err) err = (int) cudaDeviceGetAttribute(&sms,
+                cudaDevAttrMultiProcessorCount, dev);
+        if (!err && is_double)
+            err = (int) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm,
+                    es_fft_grid_rows_kernel<double, ES_FFT_THREADS>,
+                    f->rows.threads, f->rows.smem_bytes);
+        else if (!err && f->rows.threads > ES_FFT_THREADS)
+            err = (int) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm,
+                    es_fft_grid_rows_kernel<float, ES_FFT_THREADS_WIDE>,
+                    f->rows.threads, f->rows.smem_bytes);
+        else if (!err)
+            err = (int) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm,
+                    es_fft_grid_rows_kernel<float, ES_FFT_THREADS>,
+                    f->rows.threads, f->rows.smem_bytes);
+        if (per_sm < 1) per_sm = 1;
+        f->rows_grid = sms * per_sm;
+        if (!err) err = (int) cudaMalloc((void**) &f->d_row_work,
+                2 * sizeof(uint32_t));
+    }
     if (err)
     {
         (void) cudaGetLastError();
@@ -917,11 +1036,36 @@ int es_fft_create(int grid_size, int image_size, int is_double, EsFft** out)
     return 0;
 }
 
+/* (plane, tile row) list of a batch -> fft->d_row_list / d_row_work. */
+static int fft_row_list(EsFft* f, const uint32_t* occ, int nplanes,
+        const EsFftLayout& lay, cudaStream_t s)
+{
+    const int need = nplanes * lay.ntile;
+    if (need > f->row_list_cap)
+    {
+        /* grows only while the first batches of a plan are enqueued; the
+         * stream is drained because kernels may still read the old list */
+        cudaError_t err = cudaStreamSynchronize(s);
+        if (err != cudaSuccess) return (int) err;
+        if (f->d_row_list) (void) cudaFree(f->d_row_list);
+        f->d_row_list = 0;
+        f->row_list_cap = 0;
+        err = cudaMalloc((void**) &f->d_row_list, sizeof(uint32_t) * (size_t) need);
+        if (err != cudaSuccess) return (int) err;
+        f->row_list_cap = need;
+    }
+    es_fft_row_list_kernel<<<1, 1024, 0, s>>>(occ, lay, nplanes, f->d_row_list,
+            f->d_row_work);
+    return (int) cudaGetLastError();
+}
+
 void es_fft_destroy(EsFft* f)
 {
     if (!f) return;
     if (f->d_tw) (void) cudaFree(f->d_tw);
     if (f->d_bpos) (void) cudaFree(f->d_bpos);
+    if (f->d_row_list) (void) cudaFree(f->d_row_list);
+    if (f->d_row_work) (void) cudaFree(f->d_row_work);
     free(f);
 }
 
@@ -936,22 +1080,26 @@ int es_fft_grid_rows(const EsFft* f, const void* planes, int nplanes,
     cudaStream_t s = (cudaStream_t) stream;
     const EsFftLayout lay = fft_layout(f);
     const EsFftCfg& c = f->rows;
-    dim3 grid((unsigned) (f->grid_size >> c.lshift), (unsigned) nplanes);
+    /* compacted list of the occupied tile rows, then persistent CTAs */
+    EsFft* fm = const_cast<EsFft*>(f);
+    const int rc = fft_row_list(fm, occ, nplanes, lay, s);
+    if (rc) return rc;
+    dim3 grid((unsigned) f->rows_grid);
     if (f->is_double)
         es_fft_grid_rows_kernel<double, ES_FFT_THREADS><<<grid, c.threads, c.smem_bytes,
                 s>>>(f->line, (const double2*) f->d_tw, f->d_bpos,
                 (const double2*) planes, (double2*) strip, f->image_size,
-                occ, lay);
+                occ, lay, f->d_row_list, f->d_row_work);
     else if (c.threads > ES_FFT_THREADS)
         es_fft_grid_rows_kernel<float, ES_FFT_THREADS_WIDE><<<grid, c.threads, c.smem_bytes,
                 s>>>(f->line, (const float2*) f->d_tw, f->d_bpos,
                 (const float2*) planes, (float2*) strip, f->image_size,
-                occ, lay);
+                occ, lay, f->d_row_list, f->d_row_work);
     else
         es_fft_grid_rows_kernel<float, ES_FFT_THREADS><<<grid, c.threads, c.smem_bytes,
                 s>>>(f->line, (const float2*) f->d_tw, f->d_bpos,
                 (const float2*) planes, (float2*) strip, f->image_size,
-                occ, lay);
+                occ, lay, f->d_row_list, f->d_row_work);
     return (int) cudaGetLastError();
 }
 
@@ -1015,22 +1163,26 @@ int es_fft_degrid_rows(const EsFft* f, const void* strip, int nplanes,
     cudaStream_t s = (cudaStream_t) stream;
     const EsFftLayout lay = fft_layout(f);
     const EsFftCfg& c = f->rows;
-    dim3 grid((unsigned) (f->grid_size >> c.lshift), (unsigned) nplanes);
+    /* compacted list of the occupied tile rows, then persistent CTAs */
+    EsFft* fm = const_cast<EsFft*>(f);
+    const int rc = fft_row_list(fm, occ, nplanes, lay, s);
+    if (rc) return rc;
+    dim3 grid((unsigned) f->rows_grid);
     if (f->is_double)
         es_fft_degrid_rows_kernel<double, ES_FFT_THREADS><<<grid, c.threads, c.smem_bytes,
                 s>>>(f->line, (const double2*) f->d_tw, f->d_bpos,
                 (const double2*) strip, (double2*) planes, f->image_size,
-                occ, lay);
+                occ, lay, f->d_row_list, f->d_row_work);
     else if (c.threads > ES_FFT_THREADS)
         es_fft_degrid_rows_kernel<float, ES_FFT_THREADS_WIDE><<<grid, c.threads, c.smem_bytes,
                 s>>>(f->line, (const float2*) f->d_tw, f->d_bpos,
                 (const float2*) strip, (float2*) planes, f->image_size,
-                occ, lay);
+                occ, lay, f->d_row_list, f->d_row_work);
     else
         es_fft_degrid_rows_kernel<float, ES_FFT_THREADS><<<grid, c.threads, c.smem_bytes,
                 s>>>(f->line, (const float2*) f->d_tw, f->d_bpos,
                 (const float2*) strip, (float2*) planes, f->image_size,
-                occ, lay);
+                occ, lay, f->d_row_list, f->d_row_work);
     return (int) cudaGetLastError();
 }
 

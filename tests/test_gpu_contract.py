@@ -221,3 +221,16 @@ def test_three_way_with_the_reference_cuda_build(single, tmp_path):
         assert max(table["new-vs-refgpu"]) <= tol
     else:
         assert max(table["refgpu-vs-oracle64"]) <= 1e-3   # fp32 coordinates
+
+
+def test_reference_cpp_test_runs_against_this_library():
+    """The reference's own C++ test of the path
+    (tests/grid_data/test_gridder_uvw_es_fft.cpp: device arrays through
+    sdp_mem_create(..., SDP_MEM_GPU), adjointness thresholds 1e-12 / 1e-5, 45
+    argument-error cases with their codes), compiled unmodified against
+    include/ + this libska_sdp_func.so by baseline/build_ref_cpp_test.sh."""
+    exe = os.path.join(ROOT, "baseline", "_ref_cpp", "test_gridder_uvw_es_fft")
+    if not os.path.exists(exe):
+        pytest.skip("baseline/_ref_cpp not built (baseline/build_ref_cpp_test.sh)")
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, (r.stdout[-3000:], r.stderr[-3000:])
