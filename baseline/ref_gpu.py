@@ -34,7 +34,8 @@ def load_reference():
     from ska_sdp_func.utility import Lib
     assert os.path.realpath(ska_sdp_func.__file__).startswith(os.path.realpath(REF))
     Lib.handle()
-    assert os.path.realpath(Lib.find_lib()).startswith(os.path.realpath(REF)), Lib.find_lib()
+    loaded = Lib.handle()._name  # path of the CDLL the reference package opened
+    assert os.path.realpath(loaded).startswith(os.path.realpath(REF)), loaded
     return cupy, GridderUvwEsFft
 
 

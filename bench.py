@@ -488,7 +488,9 @@ def parity_check(torch, local, case, wl, dev, d_in, d_img, d_img0, d_vis_out,
     cores = host_cores(eo.lib().eso_max_threads())
     planes = info["num_total_w_grids"]
     assert o.plan["num_total_w_grids"] == planes and \
-        o.plan["grid_size"] == info["grid_size"], "oracle and product plans differ"
+        o.plan["grid_size"] == info["grid_size"] and \
+        o.plan["w_scale"] == info["w_scale"] and \
+        o.plan["min_plane_w"] == info["min_plane_w"], "oracle and product plans differ"
     lo, hi = parity_block(planes, info["grid_size"], budget_s, cores)
     tol = TOL[4 if single else 8]
     out = {"tol": tol, "planes": [lo, hi], "of_planes": planes,

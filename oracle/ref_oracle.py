@@ -77,9 +77,15 @@ def lib():
 
 
 def get_w_range(uvw, freq_hz):
-    """gridder_uvw_es_fft.py:90-106 on numpy arrays."""
-    min_abs_w = np.amin(np.abs(uvw[:, 2])) * freq_hz[0] / C_0
-    max_abs_w = np.amax(np.abs(uvw[:, 2])) * freq_hz[-1] / C_0
+    """gridder_uvw_es_fft.py:90-106, in the reference's own operation order
+    and precision (|w| extremes times (frequency / c), all in the arrays'
+    dtype): a different order moves max_abs_w by an ulp in fp32, which shifts
+    every w-plane of the lattice by ~6e-8 of its index -- 4e-5 planes at plane
+    700, enough to break 1e-5 parity between two plans that should be one."""
+    min_abs_w = np.amin(np.abs(uvw[:, 2]))
+    max_abs_w = np.amax(np.abs(uvw[:, 2]))
+    min_abs_w = min_abs_w * (freq_hz[0] / C_0)
+    max_abs_w = max_abs_w * (freq_hz[-1] / C_0)
     return float(min_abs_w), float(max_abs_w)
 
 

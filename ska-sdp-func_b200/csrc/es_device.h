@@ -182,9 +182,17 @@ int es_fft_degrid_cols(const EsFft* fft, const EsGeom* g, const void* image_t,
 int es_fft_degrid_rows(const EsFft* fft, const void* strip, int nplanes,
         void* planes, const uint32_t* occ, es_stream_t stream);
 
-/* dst[r][c] = src[c][r] (add == 0) or dst[r][c] += src[c][r], n x n reals. */
-int es_launch_transpose(const void* src, void* dst, int n, int is_double,
-        int add, es_stream_t stream);
+/* Fills the plan's w-screen table (n - 1 per pixel of one image quadrant,
+ * fp64) and chooses the fixed-point format of the phase from the largest
+ * |w| of the lattice. Call once per plan that uses w-stacking; synchronises. */
+int es_fft_set_screen(EsFft* fft, double pixel_size, double max_abs_w);
+
+/* dst[r][c] = (add == 0) or += src[c][r] x (-1)^(r + c) (/ n(r, c) when
+ * wstack != 0), N x N reals: the plane-independent factors of the w-screen
+ * are applied by the one transpose per call between the caller's image and
+ * the column-major image the line FFTs work on. */
+int es_fft_image_transpose(const EsFft* fft, const void* src, void* dst,
+        int add, int wstack, es_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -31,6 +31,7 @@
  * The arithmetic is the same DFT; the w-screen maths is that of
  * kernels.cu:110-123 with the phase reduced in fp64.
  */
+#include <math.h>
 #include <stdint.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -48,7 +49,7 @@
 #define ES_FFT_THREADS_WIDE 1024 /* variant for radices <= 16: 64 registers each,
                                   * twice the resident warps per line (fp32 only) */
 #define ES_FFT_WIDE_MAX_RADIX 16
-#define ES_FFT_MAX_SMEM (227 * 1024 - 512) /* 512 B of static occupancy flags */
+#define ES_FFT_MAX_SMEM (227 * 1024 - 576) /* static: 512 B of occupancy flags + the work item */
 
 /* CTA shape of one kernel family. */
 struct EsFftCfg
@@ -72,6 +73,11 @@ struct EsFft
     uint32_t* d_row_work; /* [0] work items of the batch, [1] next item */
     int32_t row_list_cap; /* entries */
     int32_t rows_grid;    /* resident CTAs of the row kernels on this device */
+    /* w-screen (es_fft_set_screen): n - 1 per pixel of one image quadrant */
+    double* d_nm1;        /* [image_size / 2 + 1][nm1_pitch] */
+    int32_t nm1_pitch;
+    int32_t screen_shift; /* 32 - fixed-point bits of the phase (es_screen.h) */
+    double screen_magic;
 };
 
 namespace {
@@ -90,36 +96,38 @@ __device__ __forceinline__ void load_twiddles(const T2* tw, const T2* tw_g,
     for (int i = threadIdx.x; i < count; i += blockDim.x) dst[i] = tw_g[i];
 }
 
-/* ---- w-screen: exp(sign 2 pi i w (n - 1)) / n, n = sqrt(1 - l^2 - m^2),
- * kernels.cu:110-123. The phase w (n - 1) reaches ~1e2..1e3 turns, so n - 1
- * is formed in fp64 (fp32 data: reciprocal square root seeded in fp32, one
- * Newton step in fp64 -> relative error ~1e-14) and reduced to [-0.5, 0.5]
- * turns before the fp32 sincospi. */
-template<typename T> struct Screen;
-
-template<> struct Screen<float>
+/* ---- w-screen phasor exp(sign 2 pi i w (n - 1)), n = sqrt(1 - l^2 - m^2)
+ * (kernels.cu:110-123). n - 1 comes from the plan's fp64 table (one entry per
+ * pixel of an image quadrant), the 1 / n factor and the (-1)^(i+j) shift are
+ * applied once per call by es_transpose_screen_kernel. The phase w (n - 1)
+ * reaches 1e2 .. 1e4 turns: fp32 data reduce it with one fp64 fused
+ * multiply-add into fixed point (es_screen.h), fp64 data with rint. */
+struct ScreenTab
 {
-    /* s2 = iu^2 + jv^2; w_signed = sign * w (es_screen.h) */
-    __device__ __forceinline__ static void eval(const uint32_t s2,
-            const double pix2, const float pix2f, const double w_signed,
-            float& re, float& im, float& inv_n)
+    const double* nm1;
+    int32_t pitch, shift;
+    double magic;
+};
+
+template<typename T> struct Phasor;
+
+template<> struct Phasor<float>
+{
+    __device__ __forceinline__ static void eval(const double nm1,
+            const double w_signed, const ScreenTab& tb, float& re, float& im)
     {
-        es_screen_f32(s2, pix2, pix2f, w_signed, re, im, inv_n);
+        es_phasor_f32(nm1, w_signed, tb.magic, tb.shift, re, im);
     }
 };
 
-template<> struct Screen<double>
+template<> struct Phasor<double>
 {
-    __device__ __forceinline__ static void eval(const uint32_t s2,
-            const double pix2, const float, const double w_signed,
-            double& re, double& im, double& inv_n)
+    __device__ __forceinline__ static void eval(const double nm1,
+            const double w_signed, const ScreenTab&, double& re, double& im)
     {
-        const double sos = pix2 * (double) s2;
-        const double nm1 = (-sos) / (sqrt(1.0 - sos) + 1.0);
         double t = w_signed * nm1;
         t -= rint(t);
         sincospi(2.0 * t, &im, &re);
-        inv_n = 1.0 / (nm1 + 1.0);
     }
 };
 
@@ -179,6 +187,8 @@ template<typename T2, bool WINDOW, bool ANY, bool MASK = false> struct LinearIn
         return c;
     }
     typedef T2 Raw;
+    __device__ __forceinline__ unsigned int any_bits() const { return any; }
+    __device__ __forceinline__ void merge_any(unsigned int a) { any |= a; }
     __device__ __forceinline__ T2 finish(const Cursor&, int, const T2 v) const
     {
         return v;
@@ -228,163 +238,171 @@ template<typename T2, bool WINDOW, bool MASK = false> struct LinearOut
                 (!MASK || occ_bit(bits, c.r0 + k * c.gs)))
             c.p[k * c.step] = v;
     }
+    /* nothing to prefetch */
+    struct Pre {};
+    __device__ __forceinline__ Pre prefetch(const Cursor&, int) const
+    {
+        return Pre();
+    }
+    __device__ __forceinline__ void store1(const Cursor& c, int k, const T2 v,
+            const Pre) const
+    {
+        store(c, k, v);
+    }
     __device__ __forceinline__ void store2(const Cursor& c, int k, const T2 v0,
-            const T2 v1) const
+            const T2 v1, const Pre, const Pre) const
     {
         store(c, k, v0);
         store(c, k + 1, v1);
     }
 };
 
-/* gridding pass 2 output: w-screen and sum into imageT (kernels.cu:444-515) */
+/* gridding pass 2 output: w-screen phasor and sum into imageT
+ * (kernels.cu:444-515; 1 / n and the shift sign: es_transpose_screen_kernel) */
 template<typename T, typename T2> struct ScreenOut
 {
     struct Cursor
     {
-        T* p;        /* imageT element of (line, iu0) */
-        int iu0, gs, jv;
-        uint32_t jv2;
+        T* p;              /* imageT element of (line, iu0) */
+        const double* tab; /* n - 1 of (|jv|, 0) */
+        int iu0, gs;
     };
     T* image_t;      /* imageT + first column of the bundle * n + n / 2 */
     int n, half, gh; /* image size, n / 2, grid_size / 2 */
     int jv0;         /* first column - n / 2 */
     int wstack;
-    double pix2, w;
-    float pix2f;
+    double w;        /* sign * w of the plane */
+    ScreenTab tb;
     __device__ __forceinline__ Cursor cursor(int line, int idx0, int gs) const
     {
         Cursor c;
         c.iu0 = idx0 - gh;
         c.gs = gs;
-        c.jv = jv0 + line;
-        c.jv2 = (uint32_t) (c.jv * c.jv);
+        c.tab = tb.nm1 + (size_t) abs(jv0 + line) * tb.pitch;
         c.p = image_t + (ptrdiff_t) line * n + c.iu0;
         return c;
     }
-    __device__ __forceinline__ void store(const Cursor& c, int k, const T2 v) const
+    /* n - 1 of output k, loaded before the butterfly arithmetic */
+    typedef double Pre;
+    __device__ __forceinline__ Pre prefetch(const Cursor& c, int k) const
+    {
+        const int iu = c.iu0 + k * c.gs;
+        double nm1 = 0.0;
+        if (wstack && (unsigned) (iu + half) < (unsigned) n)
+            nm1 = __ldg(c.tab + abs(iu));
+        return nm1;
+    }
+    __device__ __forceinline__ void store1(const Cursor& c, int k, const T2 v,
+            const Pre nm1) const
     {
         const int iu = c.iu0 + k * c.gs;
         if ((unsigned) (iu + half) >= (unsigned) n) return;
         T val = v.x;
         if (wstack)
         {
-            /* iu^2 + jv^2 < 2^31 for images up to 32768^2 */
-            T cr, ci, inv_n;
-            Screen<T>::eval((uint32_t) (iu * iu) + c.jv2, pix2, pix2f, -w,
-                    cr, ci, inv_n);
-            val = (v.x * cr - v.y * ci) * inv_n;
+            T cr, ci;
+            Phasor<T>::eval(nm1, w, tb, cr, ci);
+            val = v.x * cr - v.y * ci;
         }
-        if ((iu + c.jv) & 1) val = -val;
         atomicAdd(c.p + k * c.gs, val);
     }
     /* outputs k and k + 1: when both fall into the image (the common case)
      * the two phasors are evaluated side by side without a branch between */
     __device__ __forceinline__ void store2(const Cursor& c, int k, const T2 v0,
-            const T2 v1) const
+            const T2 v1, const Pre nm0, const Pre nm1) const
     {
         const int iu0 = c.iu0 + k * c.gs, iu1 = iu0 + c.gs;
         const bool in0 = (unsigned) (iu0 + half) < (unsigned) n;
         const bool in1 = (unsigned) (iu1 + half) < (unsigned) n;
         if (!(in0 && in1) || !wstack)
         {
-            if (in0) store(c, k, v0);
-            if (in1) store(c, k + 1, v1);
+            if (in0) store1(c, k, v0, nm0);
+            if (in1) store1(c, k + 1, v1, nm1);
             return;
         }
-        T cr0, ci0, inv0, cr1, ci1, inv1;
-        Screen<T>::eval((uint32_t) (iu0 * iu0) + c.jv2, pix2, pix2f, -w,
-                cr0, ci0, inv0);
-        Screen<T>::eval((uint32_t) (iu1 * iu1) + c.jv2, pix2, pix2f, -w,
-                cr1, ci1, inv1);
-        T val0 = (v0.x * cr0 - v0.y * ci0) * inv0;
-        T val1 = (v1.x * cr1 - v1.y * ci1) * inv1;
-        if ((iu0 + c.jv) & 1) val0 = -val0;
-        if ((iu1 + c.jv) & 1) val1 = -val1;
-        atomicAdd(c.p + k * c.gs, val0);
-        atomicAdd(c.p + (k + 1) * c.gs, val1);
+        T cr0, ci0, cr1, ci1;
+        Phasor<T>::eval(nm0, w, tb, cr0, ci0);
+        Phasor<T>::eval(nm1, w, tb, cr1, ci1);
+        atomicAdd(c.p + k * c.gs, v0.x * cr0 - v0.y * ci0);
+        atomicAdd(c.p + (k + 1) * c.gs, v1.x * cr1 - v1.y * ci1);
     }
 };
 
-/* degridding pass 1 input: imageT x conj w-screen, zero outside the image
- * (kernels.cu:580-676) */
+/* degridding pass 1 input: imageT (already x shift sign / n) x conj w-screen
+ * phasor, zero outside the image (kernels.cu:580-676) */
 template<typename T, typename T2> struct ScreenIn
 {
     struct Cursor
     {
         const T* p;
-        int iu0, gs, jv;
-        uint32_t jv2;
+        const double* tab;
+        int iu0, gs;
     };
     const T* image_t;
     int n, half, gh, jv0, wstack;
-    double pix2, w;
-    float pix2f;
+    double w;
+    ScreenTab tb;
     __device__ __forceinline__ Cursor cursor(int line, int idx0, int gs) const
     {
         Cursor c;
         c.iu0 = idx0 - gh;
         c.gs = gs;
-        c.jv = jv0 + line;
-        c.jv2 = (uint32_t) (c.jv * c.jv);
+        c.tab = tb.nm1 + (size_t) abs(jv0 + line) * tb.pitch;
         c.p = image_t + (ptrdiff_t) line * n + c.iu0;
         return c;
     }
-    typedef T Raw;
-    /* the image value (0 outside the image); no arithmetic yet */
-    __device__ __forceinline__ T fetch(const Cursor& c, int k) const
+    struct Raw
+    {
+        T d;
+        double nm1;
+    };
+    __device__ __forceinline__ unsigned int any_bits() const { return 0u; }
+    __device__ __forceinline__ void merge_any(unsigned int) {}
+    /* the image value (0 outside the image) and n - 1; no arithmetic yet */
+    __device__ __forceinline__ Raw fetch(const Cursor& c, int k) const
     {
         const int iu = c.iu0 + k * c.gs;
-        T d = 0;
-        if ((unsigned) (iu + half) < (unsigned) n) d = c.p[k * c.gs];
-        return d;
+        Raw r;
+        r.d = 0;
+        r.nm1 = 0.0;
+        if ((unsigned) (iu + half) < (unsigned) n)
+        {
+            r.d = c.p[k * c.gs];
+            if (wstack) r.nm1 = __ldg(c.tab + abs(iu));
+        }
+        return r;
     }
-    __device__ __forceinline__ T2 finish(const Cursor& c, int k, T d) const
+    __device__ __forceinline__ T2 finish(const Cursor& c, int k, const Raw r) const
     {
         T2 o;
-        o.x = 0; o.y = 0;
+        o.x = r.d; o.y = 0;
         const int iu = c.iu0 + k * c.gs;
-        if ((unsigned) (iu + half) >= (unsigned) n) return o;
-        if ((iu + c.jv) & 1) d = -d;
-        if (wstack)
+        if (wstack && (unsigned) (iu + half) < (unsigned) n)
         {
-            T cr, ci, inv_n;
-            Screen<T>::eval((uint32_t) (iu * iu) + c.jv2, pix2, pix2f, w,
-                    cr, ci, inv_n);
-            d *= inv_n;
-            o.x = cr * d;
-            o.y = ci * d;
-        }
-        else
-        {
-            o.x = d;
+            T cr, ci;
+            Phasor<T>::eval(r.nm1, w, tb, cr, ci);
+            o.x = cr * r.d;
+            o.y = ci * r.d;
         }
         return o;
     }
-    /* elements k and k + 1: both inside the image (the common case) -> the
-     * two phasors are evaluated side by side without a branch between */
-    __device__ __forceinline__ void finish2(const Cursor& c, int k, T d0, T d1,
-            T2& o0, T2& o1) const
+    /* elements k and k + 1: the two phasors are evaluated side by side
+     * without a branch between (outside the image d == 0 and n - 1 == 0:
+     * the products are zeros) */
+    __device__ __forceinline__ void finish2(const Cursor& c, int k, const Raw r0,
+            const Raw r1, T2& o0, T2& o1) const
     {
-        const int iu0 = c.iu0 + k * c.gs, iu1 = iu0 + c.gs;
-        const bool in0 = (unsigned) (iu0 + half) < (unsigned) n;
-        const bool in1 = (unsigned) (iu1 + half) < (unsigned) n;
-        if (!(in0 && in1) || !wstack)
+        if (!wstack)
         {
-            o0 = finish(c, k, d0);
-            o1 = finish(c, k + 1, d1);
+            o0.x = r0.d; o0.y = 0;
+            o1.x = r1.d; o1.y = 0;
             return;
         }
-        T cr0, ci0, inv0, cr1, ci1, inv1;
-        Screen<T>::eval((uint32_t) (iu0 * iu0) + c.jv2, pix2, pix2f, w,
-                cr0, ci0, inv0);
-        Screen<T>::eval((uint32_t) (iu1 * iu1) + c.jv2, pix2, pix2f, w,
-                cr1, ci1, inv1);
-        if ((iu0 + c.jv) & 1) d0 = -d0;
-        if ((iu1 + c.jv) & 1) d1 = -d1;
-        d0 *= inv0;
-        d1 *= inv1;
-        o0.x = cr0 * d0; o0.y = ci0 * d0;
-        o1.x = cr1 * d1; o1.y = ci1 * d1;
+        T cr0, ci0, cr1, ci1;
+        Phasor<T>::eval(r0.nm1, w, tb, cr0, ci0);
+        Phasor<T>::eval(r1.nm1, w, tb, cr1, ci1);
+        o0.x = cr0 * r0.d; o0.y = ci0 * r0.d;
+        o1.x = cr1 * r1.d; o1.y = ci1 * r1.d;
     }
 };
 
@@ -414,6 +432,7 @@ struct EsFftLayout
     int64_t plane_elems; /* elements of T per plane (grid_size x image_size) */
     int32_t ntile, occ_nw; /* occupancy words: es_device.h */
     int32_t rows_twg, cols_twg; /* twiddles read from global memory */
+    ScreenTab screen;  /* w-screen table of the plan (es_fft_set_screen) */
 };
 
 /* Words of plane q: tile bits of tile row tu at + tu * nw, the tile-row bits
@@ -625,8 +644,7 @@ es_fft_grid_cols_screen_kernel(const EsFftLine pl,
     out.gh = gsz / 2;
     out.jv0 = col0 - n / 2;
     out.wstack = g.do_wstacking;
-    out.pix2 = g.pixel_size * g.pixel_size;
-    out.pix2f = (float) out.pix2;
+    out.tb = lay.screen;
     load_twiddles(tw, tw_g, pl.num_twiddles);
     for (int q = 0; q < nplanes; ++q)
     {
@@ -636,7 +654,8 @@ es_fft_grid_cols_screen_kernel(const EsFftLine pl,
         if (!occ_fetch(s_bits, occ_plane(occ, lay, q) +
                 lay.ntile * lay.occ_nw, lay.occ_nw)) continue;
         in.base = strip + (size_t) q * lay.plane_elems + col0;
-        out.w = (double) (first_plane + q) * g.inv_w_scale + g.min_plane_w;
+        /* gridding: exp(-2 pi i w (n - 1)) */
+        out.w = -((double) (first_plane + q) * g.inv_w_scale + g.min_plane_w);
         for (int step = 0; step < pl.num_stages; ++step)
         {
             if (step > 0) __syncthreads();
@@ -686,8 +705,7 @@ __global__ void __launch_bounds__(MAXT, 1) es_fft_degrid_cols_kernel(
     in.gh = gsz / 2;
     in.jv0 = col0 - n / 2;
     in.wstack = g.do_wstacking;
-    in.pix2 = g.pixel_size * g.pixel_size;
-    in.pix2f = (float) in.pix2;
+    in.tb = lay.screen;
     in.w = (double) (first_plane + q) * g.inv_w_scale + g.min_plane_w;
     LinearOut<T2, false, true> out;
     out.bits = s_bits;
@@ -753,10 +771,15 @@ __global__ void __launch_bounds__(MAXT, 1) es_fft_degrid_rows_kernel(
 
 /* ------------------------------------------------------ image transposes */
 
-/* dst[r][c] (+)= src[c][r], square n x n. */
+/* dst[r][c] (+)= src[c][r] x (-1)^(r + c) / n(r, c), square n x n: the
+ * transposes between the caller's image and the column-major accumulator /
+ * model copy the line FFTs work on carry the two per-pixel factors of the
+ * w-screen that do not depend on the plane (kernels.cu:119,499-507: xn and
+ * the shift sign). tab == 0 (no w-stacking): the sign only. */
 template<typename T, bool ADD>
-__global__ void __launch_bounds__(256) es_transpose_kernel(
-        const T* __restrict__ src, T* __restrict__ dst, const int n)
+__global__ void __launch_bounds__(256) es_transpose_screen_kernel(
+        const T* __restrict__ src, T* __restrict__ dst, const int n,
+        const double* __restrict__ tab, const int pitch)
 {
     __shared__ T t[32][33];
     const int bx = blockIdx.x * 32, by = blockIdx.y * 32;
@@ -766,15 +789,33 @@ __global__ void __launch_bounds__(256) es_transpose_kernel(
         if (r < n && c < n) t[k][threadIdx.x] = src[(size_t) r * n + c];
     }
     __syncthreads();
+    const int half = n / 2;
     for (int k = threadIdx.y; k < 32; k += 8)
     {
         const int r = bx + k, c = by + threadIdx.x;
         if (r < n && c < n)
         {
-            if (ADD) dst[(size_t) r * n + c] += t[threadIdx.x][k];
-            else dst[(size_t) r * n + c] = t[threadIdx.x][k];
+            T v = t[threadIdx.x][k];
+            if (tab)
+                v = (T) ((double) v / (tab[(size_t) abs(r - half) * pitch +
+                        abs(c - half)] + 1.0));
+            if ((r + c) & 1) v = -v;
+            if (ADD) dst[(size_t) r * n + c] += v;
+            else dst[(size_t) r * n + c] = v;
         }
     }
+}
+
+/* tab[j][i] = n - 1 at l = i pixel_size, m = j pixel_size (fp64). */
+__global__ void __launch_bounds__(256) es_screen_table_kernel(
+        double* __restrict__ tab, const int count, const int pitch,
+        const double pix2)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y;
+    if (i < count)
+        tab[(size_t) j * pitch + i] = es_screen_nm1((uint32_t) (i * i + j * j),
+                pix2);
 }
 
 } // namespace
@@ -845,12 +886,25 @@ EsFftLayout fft_layout(const EsFft* f)
     lay.plane_elems = f->plane_elems;
     lay.ntile = (f->grid_size + ES_TILE - 1) / ES_TILE;
     lay.occ_nw = (lay.ntile + 31) >> 5;
+    lay.screen.nm1 = f->d_nm1;
+    lay.screen.pitch = f->nm1_pitch;
+    lay.screen.shift = f->screen_shift;
+    lay.screen.magic = f->screen_magic;
     return lay;
 }
 
 template<typename K>
 int fft_set_smem(K kernel, size_t bytes)
 {
+    /* the opt-in limit of the device covers static + dynamic shared memory */
+    cudaFuncAttributes attr;
+    int dev = 0, optin = 0;
+    if (cudaFuncGetAttributes(&attr, (const void*) kernel) == cudaSuccess &&
+            cudaGetDevice(&dev) == cudaSuccess &&
+            cudaDeviceGetAttribute(&optin,
+            cudaDevAttrMaxSharedMemoryPerBlockOptin, dev) == cudaSuccess &&
+            bytes + attr.sharedSizeBytes > (size_t) optin)
+        bytes = (size_t) optin - attr.sharedSizeBytes;
     return (int) cudaFuncSetAttribute((const void*) kernel,
             cudaFuncAttributeMaxDynamicSharedMemorySize, (int) bytes);
 }
@@ -1066,6 +1120,7 @@ void es_fft_destroy(EsFft* f)
     if (f->d_bpos) (void) cudaFree(f->d_bpos);
     if (f->d_row_list) (void) cudaFree(f->d_row_list);
     if (f->d_row_work) (void) cudaFree(f->d_row_work);
+    if (f->d_nm1) (void) cudaFree(f->d_nm1);
     free(f);
 }
 
@@ -1186,26 +1241,55 @@ int es_fft_degrid_rows(const EsFft* f, const void* strip, int nplanes,
     return (int) cudaGetLastError();
 }
 
-int es_launch_transpose(const void* src, void* dst, int n, int is_double,
-        int add, es_stream_t stream)
+int es_fft_image_transpose(const EsFft* f, const void* src, void* dst,
+        int add, int wstack, es_stream_t stream)
 {
     cudaStream_t s = (cudaStream_t) stream;
+    const int n = f->image_size;
+    const double* tab = wstack ? f->d_nm1 : 0;
+    if (wstack && !tab) return (int) cudaErrorInvalidValue;
     dim3 block(32, 8), grid((unsigned) ((n + 31) / 32), (unsigned) ((n + 31) / 32));
-    if (is_double)
+    if (f->is_double)
     {
-        if (add) es_transpose_kernel<double, true><<<grid, block, 0, s>>>(
-                (const double*) src, (double*) dst, n);
-        else es_transpose_kernel<double, false><<<grid, block, 0, s>>>(
-                (const double*) src, (double*) dst, n);
+        if (add) es_transpose_screen_kernel<double, true><<<grid, block, 0, s>>>(
+                (const double*) src, (double*) dst, n, tab, f->nm1_pitch);
+        else es_transpose_screen_kernel<double, false><<<grid, block, 0, s>>>(
+                (const double*) src, (double*) dst, n, tab, f->nm1_pitch);
     }
     else
     {
-        if (add) es_transpose_kernel<float, true><<<grid, block, 0, s>>>(
-                (const float*) src, (float*) dst, n);
-        else es_transpose_kernel<float, false><<<grid, block, 0, s>>>(
-                (const float*) src, (float*) dst, n);
+        if (add) es_transpose_screen_kernel<float, true><<<grid, block, 0, s>>>(
+                (const float*) src, (float*) dst, n, tab, f->nm1_pitch);
+        else es_transpose_screen_kernel<float, false><<<grid, block, 0, s>>>(
+                (const float*) src, (float*) dst, n, tab, f->nm1_pitch);
     }
     return (int) cudaGetLastError();
+}
+
+int es_fft_set_screen(EsFft* f, double pixel_size, double max_abs_w)
+{
+    const int count = f->image_size / 2 + 1;
+    const int pitch = (count + 3) & ~3;
+    if (!f->d_nm1)
+    {
+        cudaError_t err = cudaMalloc((void**) &f->d_nm1,
+                sizeof(double) * (size_t) count * (size_t) pitch);
+        if (err != cudaSuccess) return (int) err;
+    }
+    f->nm1_pitch = pitch;
+    const double pix2 = pixel_size * pixel_size;
+    /* largest |w (n - 1)| of the plan, in turns: the corner pixel */
+    const double half = 0.5 * (double) f->image_size;
+    const double sos = 2.0 * pix2 * half * half;
+    const double nm1_max = sos / (sqrt(sos < 1.0 ? 1.0 - sos : 0.0) + 1.0);
+    const int bits = es_screen_fixed_bits(fabs(max_abs_w) * nm1_max);
+    f->screen_shift = 32 - bits;
+    f->screen_magic = es_screen_magic(bits);
+    dim3 grid((unsigned) ((count + 255) / 256), (unsigned) count);
+    es_screen_table_kernel<<<grid, 256>>>(f->d_nm1, count, pitch, pix2);
+    cudaError_t err = cudaGetLastError();
+    if (err == cudaSuccess) err = cudaDeviceSynchronize();
+    return (int) err;
 }
 
 } // extern "C"

@@ -72,7 +72,7 @@ template<typename T2, typename T> ES_HD T2 es_caxpy(const T2 c, const T2 a,
     T2 r; r.x = c.x + a.x * s; r.y = c.y + a.y * s; return r;
 }
 
-#if defined(__CUDACC__)
+#if defined(__CUDACC__) && !defined(ES_FFT_NO_PACKED)
 /* fp32 on sm_100a: the fma pipe issues one instruction per two cycles and
  * scheduler, scalar or packed, so complex arithmetic goes through the packed
  * forms FADD2 / FMUL2 / FFMA2 on (re, im) register pairs. The operand swap,
@@ -380,19 +380,50 @@ ES_HD void es_bf_core(T2 (&v)[R], const EsFftStage& st, const T2* tw,
     }
 }
 
+/* What one pass needs from the line plan, by value (the pass functions may
+ * be real calls: no references to the kernel's parameter space). */
+struct EsFftPassArgs
+{
+    EsFftStage st;
+    int32_t n, pad;
+    float inv_stride0; /* 1 / stage[0].stride */
+};
+
 /* Position of element `pos` of a line in (shared) memory: one pad of
- * pl.pad elements after every block of pl.stage[0].stride elements, so that
+ * pad elements after every block of stage[0].stride elements, so that
  * the digit-reversed last pass (consecutive threads stage[0].stride elements
  * apart) is free of bank conflicts. */
-ES_HD int es_padded(const EsFftLine& pl, const int pos)
+ES_HD int es_padded(const EsFftPassArgs& pa, const int pos)
 {
-    if (pl.pad == 0) return pos;
-    return pos + pl.pad * (int) (((float) pos + 0.5f) * pl.inv_stride0);
+    if (pa.pad == 0) return pos;
+    return pos + pa.pad * (int) (((float) pos + 0.5f) * pa.inv_stride0);
 }
 
+/* Largest radix whose output-functor operands are loaded before the
+ * butterfly arithmetic (es_line_pass_body). */
+#ifndef ES_FFT_PREFETCH_MAX_RADIX
+#define ES_FFT_PREFETCH_MAX_RADIX 11
+#endif
+
+/* Position of a stage in the stage list: it fixes the addressing pattern and,
+ * with the flow graph, whether the pass reads from `in` / writes to `out`. */
+#define ES_FFT_KIND_FIRST 0  /* stage 0 of several */
+#define ES_FFT_KIND_MIDDLE 1
+#define ES_FFT_KIND_LAST 2   /* last stage of several */
+#define ES_FFT_KIND_ONLY 3   /* single-stage line */
+
+/* The pass functions are real device functions, one per (radix, kind), so
+ * that each gets its own register allocation: inlined into one kernel the
+ * ~60 of them share the worst case and spill (ptxas -v: 1 - 2.5 KB of spill
+ * stores in the column kernels), -DES_FFT_PASS_INLINE restores that form. */
+#if defined(__CUDACC__) && !defined(ES_FFT_PASS_INLINE)
+#define ES_PASS_FN __device__ __noinline__
+#else
+#define ES_PASS_FN ES_HD
+#endif
+
 /* One pass of the line FFT over `1 << lshift` lines (pitch elements apart in
- * x) by nthreads workers, this one being tid. step = 0 .. num_stages - 1 in
- * processing order (DIF: stage = step, DIT: stage = num_stages - 1 - step).
+ * x) by nthreads workers, this one being tid.
  *  - the first processed pass takes its inputs from `in` instead of x, the
  *    last one hands its outputs to `out`; both are addressed through a cursor
  *    c = cursor(line, index0, index_stride), element k of the butterfly being
@@ -403,19 +434,27 @@ ES_HD int es_padded(const EsFftLine& pl, const int pos)
  *      consecutive butterflies t own consecutive indices and bpos[t] is the
  *      padded position of their `radix` contiguous elements in x;
  *  - all other traffic is in place in x (no barrier inside a pass).
- * The caller synchronises between passes. */
-template<int R, int SGN, bool DIT, typename T, typename T2, typename In,
-        typename Out>
-ES_HD void es_line_pass_body(T2* x, const EsFftLine& pl, const int stage,
-        const bool from_in, const bool to_out, const T2* tw,
-        const int32_t* bpos, const int lshift, const int pitch, const int tid,
-        const int nthreads, In& in, Out& out)
+ * The caller synchronises between passes. Returns in.any_bits(). */
+template<int R, int SGN, bool DIT, int KIND, typename T, typename T2,
+        typename In, typename Out>
+ES_PASS_FN unsigned int es_line_pass_body(T2* x, const EsFftPassArgs pa,
+        const T2* tw, const int32_t* bpos, const int lshift, const int pitch,
+        const int tid, const int nthreads, In in, Out out)
 {
-    const EsFftStage& st = pl.stage[stage];
-    const int per_line = pl.n / R;
+#if defined(__CUDA_ARCH__)
+    __builtin_assume(__isShared(x));
+#endif
+    constexpr bool first_stage = (KIND == ES_FFT_KIND_FIRST ||
+            KIND == ES_FFT_KIND_ONLY);
+    constexpr bool last_stage = (KIND == ES_FFT_KIND_LAST ||
+            KIND == ES_FFT_KIND_ONLY);
+    /* processing order: DIF stage 0 first, DIT last stage first */
+    constexpr bool from_in = DIT ? last_stage : first_stage;
+    constexpr bool to_out = DIT ? first_stage : last_stage;
+    const EsFftStage& st = pa.st;
+    const int per_line = pa.n / R;
     const int total = per_line << lshift;
     const int lmask = (1 << lshift) - 1;
-    const bool last_stage = (stage == pl.num_stages - 1);
     for (int e = tid; e < total; e += nthreads)
     {
         const int line = e & lmask, ql = e >> lshift;
@@ -432,25 +471,24 @@ ES_HD void es_line_pass_body(T2* x, const EsFftLine& pl, const int stage,
         else
         {
             int b;
-            if (stage == 0) { b = 0; j = ql; }
+            if (first_stage) { b = 0; j = ql; }
             else
             {
                 b = (int) (((float) ql + 0.5f) * st.inv_stride);
                 j = ql - b * st.stride;
             }
             const int pos = b * st.len + j;
-            base = es_padded(pl, pos);
+            base = es_padded(pa, pos);
             /* stage 0 strides over the pads, later stages stay inside a block */
-            estride = (stage == 0) ? st.stride + pl.pad : st.stride;
+            estride = first_stage ? st.stride + pa.pad : st.stride;
             gidx = j; /* only used by stage 0 */
             gstride = st.stride;
         }
         T2 v[R];
-        if (from_in)
+        if constexpr (from_in)
         {
             /* two phases so that all R loads are in flight before the first
-             * value is used (the w-screen input functor does ~80 instructions
-             * of arithmetic per element) */
+             * value is used */
             const typename In::Cursor c = in.cursor(line, gidx, gstride);
             typename In::Raw raw[R];
 #pragma unroll
@@ -465,26 +503,52 @@ ES_HD void es_line_pass_body(T2* x, const EsFftLine& pl, const int stage,
 #pragma unroll
             for (int k = 0; k < R; ++k) v[k] = xl[base + k * estride];
         }
-        es_bf_core<R, SGN, DIT, T>(v, st, tw, j);
-        if (to_out)
+        if constexpr (to_out)
         {
-            const typename Out::Cursor c = out.cursor(line, gidx, gstride);
+            /* the output functor may load per-output operands (the w-screen
+             * table) before the butterfly arithmetic; large radices load
+             * them afterwards to stay inside the register file */
+            const typename Out::Cursor oc = out.cursor(line, gidx, gstride);
+            constexpr bool early = (R <= ES_FFT_PREFETCH_MAX_RADIX);
+            typename Out::Pre pre[early ? R : 1];
+            if constexpr (early)
+            {
+#pragma unroll
+                for (int k = 0; k < R; ++k) pre[k] = out.prefetch(oc, k);
+            }
+            es_bf_core<R, SGN, DIT, T>(v, st, tw, j);
             /* two outputs per call: the w-screen output functor evaluates
              * both phasors in one straight-line block (instruction-level
              * parallelism for its long dependent chains) */
 #pragma unroll
             for (int k = 0; k + 1 < R; k += 2)
-                out.store2(c, k, v[es_out_slot<R>(k)],
-                        v[es_out_slot<R>(k + 1)]);
-            if (R & 1) out.store(c, R - 1, v[es_out_slot<R>(R - 1)]);
+            {
+                if constexpr (early)
+                    out.store2(oc, k, v[es_out_slot<R>(k)],
+                            v[es_out_slot<R>(k + 1)], pre[k], pre[k + 1]);
+                else
+                    out.store2(oc, k, v[es_out_slot<R>(k)],
+                            v[es_out_slot<R>(k + 1)], out.prefetch(oc, k),
+                            out.prefetch(oc, k + 1));
+            }
+            if (R & 1)
+            {
+                if constexpr (early)
+                    out.store1(oc, R - 1, v[es_out_slot<R>(R - 1)], pre[R - 1]);
+                else
+                    out.store1(oc, R - 1, v[es_out_slot<R>(R - 1)],
+                            out.prefetch(oc, R - 1));
+            }
         }
         else
         {
+            es_bf_core<R, SGN, DIT, T>(v, st, tw, j);
 #pragma unroll
             for (int k = 0; k < R; ++k)
                 xl[base + k * estride] = v[es_out_slot<R>(k)];
         }
     }
+    return in.any_bits();
 }
 
 /* fp64 butterflies above radix 16 do not fit the register file and are
@@ -493,15 +557,31 @@ ES_HD void es_line_pass_body(T2* x, const EsFftLine& pl, const int stage,
 
 template<int R, int SGN, bool DIT, int MAXR, typename T, typename T2,
         typename In, typename Out>
-ES_HD void es_line_pass_r(T2* x, const EsFftLine& pl, const int stage,
-        const bool from_in, const bool to_out, const T2* tw,
-        const int32_t* bpos, const int lshift, const int pitch, const int tid,
-        const int nthreads, In& in, Out& out)
+ES_HD unsigned int es_line_pass_r(T2* x, const EsFftPassArgs& pa,
+        const int kind, const T2* tw, const int32_t* bpos, const int lshift,
+        const int pitch, const int tid, const int nthreads, const In& in,
+        const Out& out)
 {
     if constexpr ((sizeof(T) == 4 || R <= ES_FFT_MAX_RADIX_DOUBLE) &&
             R <= MAXR)
-        es_line_pass_body<R, SGN, DIT, T>(x, pl, stage, from_in, to_out, tw,
-                bpos, lshift, pitch, tid, nthreads, in, out);
+    {
+        switch (kind)
+        {
+        case ES_FFT_KIND_FIRST:
+            return es_line_pass_body<R, SGN, DIT, ES_FFT_KIND_FIRST, T>(x, pa,
+                    tw, bpos, lshift, pitch, tid, nthreads, in, out);
+        case ES_FFT_KIND_MIDDLE:
+            return es_line_pass_body<R, SGN, DIT, ES_FFT_KIND_MIDDLE, T>(x, pa,
+                    tw, bpos, lshift, pitch, tid, nthreads, in, out);
+        case ES_FFT_KIND_LAST:
+            return es_line_pass_body<R, SGN, DIT, ES_FFT_KIND_LAST, T>(x, pa,
+                    tw, bpos, lshift, pitch, tid, nthreads, in, out);
+        default:
+            return es_line_pass_body<R, SGN, DIT, ES_FFT_KIND_ONLY, T>(x, pa,
+                    tw, bpos, lshift, pitch, tid, nthreads, in, out);
+        }
+    }
+    return 0u;
 }
 
 /* Radices with a butterfly (ES_FFT_CASE is defined at the point of use). */
@@ -514,8 +594,10 @@ ES_HD void es_line_pass_r(T2* x, const EsFftLine& pl, const int stage,
     ES_FFT_CASE(24) ES_FFT_CASE(28) ES_FFT_CASE(32)
 #endif
 
-/* MAXR: largest radix instantiated (kernel variants with more threads and
- * fewer registers per thread carry only the small butterflies). */
+/* step = 0 .. num_stages - 1 in processing order (DIF: stage = step, DIT:
+ * stage = num_stages - 1 - step). MAXR: largest radix instantiated (kernel
+ * variants with more threads and fewer registers per thread carry only the
+ * small butterflies). */
 template<int SGN, bool DIT, typename T, int MAXR = 32, typename T2, typename In,
         typename Out>
 ES_HD void es_line_pass(T2* x, const EsFftLine& pl, const int step,
@@ -523,15 +605,24 @@ ES_HD void es_line_pass(T2* x, const EsFftLine& pl, const int step,
         const int tid, const int nthreads, In& in, Out& out)
 {
     const int stage = DIT ? pl.num_stages - 1 - step : step;
-    const bool from_in = (step == 0), to_out = (step == pl.num_stages - 1);
-#define ES_FFT_CASE(R) case R: es_line_pass_r<R, SGN, DIT, MAXR, T>(x, pl, stage, \
-        from_in, to_out, tw, bpos, lshift, pitch, tid, nthreads, in, out); break;
-    switch (pl.stage[stage].radix)
+    const int kind = pl.num_stages == 1 ? ES_FFT_KIND_ONLY :
+            stage == 0 ? ES_FFT_KIND_FIRST :
+            stage == pl.num_stages - 1 ? ES_FFT_KIND_LAST : ES_FFT_KIND_MIDDLE;
+    EsFftPassArgs pa;
+    pa.st = pl.stage[stage];
+    pa.n = pl.n;
+    pa.pad = pl.pad;
+    pa.inv_stride0 = pl.inv_stride0;
+    unsigned int any = 0u;
+#define ES_FFT_CASE(R) case R: any = es_line_pass_r<R, SGN, DIT, MAXR, T>(x, pa, \
+        kind, tw, bpos, lshift, pitch, tid, nthreads, in, out); break;
+    switch (pa.st.radix)
     {
     ES_FFT_RADIX_CASES
     default: break;
     }
 #undef ES_FFT_CASE
+    in.merge_any(any);
 }
 
 #endif

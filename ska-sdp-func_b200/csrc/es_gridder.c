@@ -503,11 +503,21 @@ sdp_GridderUvwEsFft* sdp_gridder_uvw_es_fft_create_plan(
     {
         const int rc = es_fft_create(g->grid_size, g->image_size, is_double,
                 &plan->pruned_fft);
-        if (rc > 0)
+        int rc2 = 0;
+        if (rc == 0 && plan->pruned_fft && g->do_wstacking)
+        {
+            /* w-screen table of the fused column passes */
+            const double w_lo = fabs(g->min_plane_w);
+            const double w_hi = fabs(g->min_plane_w +
+                    (double) (g->num_planes - 1) * g->inv_w_scale);
+            rc2 = es_fft_set_screen(plan->pruned_fft, g->pixel_size,
+                    w_lo > w_hi ? w_lo : w_hi);
+        }
+        if (rc > 0 || rc2 > 0)
         {
             *status = SDP_ERR_MEM_ALLOC_FAILURE;
             SDP_LOG_CRITICAL("GPU memory allocation failure: %s",
-                    cudaGetErrorString((cudaError_t) rc));
+                    cudaGetErrorString((cudaError_t) (rc > 0 ? rc : rc2)));
         }
     }
     if (!*status)
@@ -1165,8 +1175,8 @@ void sdp_grid_uvw_es_fft(sdp_GridderUvwEsFft* plan, const sdp_Mem* uvw,
     {
         /* dirty += transpose(accumulator) */
         late_copy_wait(plan, &a);
-        ES_CUDA(es_launch_transpose(plan->image_t.ptr, a.dirty,
-                g->image_size, g->is_double, 1, s));
+        ES_CUDA(es_fft_image_transpose(plan->pruned_fft, plan->image_t.ptr,
+                a.dirty, 1, g->do_wstacking, s));
         plan->stats.kernel_launches += 1;
     }
     event_mark(plan, 2);
@@ -1234,8 +1244,8 @@ void sdp_ifft_degrid_uvw_es(sdp_GridderUvwEsFft* plan, const sdp_Mem* uvw,
     if (plan->pruned_fft)
     {
         /* the line FFTs read image columns: transposed copy, once */
-        ES_CUDA(es_launch_transpose(a.dirty, plan->image_t.ptr,
-                g->image_size, g->is_double, 0, s));
+        ES_CUDA(es_fft_image_transpose(plan->pruned_fft, a.dirty,
+                plan->image_t.ptr, 0, g->do_wstacking, s));
         plan->stats.kernel_launches += 1;
     }
     const int batch = even_batch(plan, g->plane_end - g->plane_begin);

@@ -188,4 +188,57 @@ ES_SCR_HD void es_screen_f32(const uint32_t s, const double pix2,
 #endif
 }
 
+/* ---- table form (es_fft.cu): n - 1 per image pixel comes from a table that
+ * the plan fills once in full fp64 (it depends on |iu|, |jv| and the pixel
+ * size only), 1 / n and the (-1)^(i+j) shift are applied once per call by the
+ * image transposes, so that per (pixel, w-plane) only the phasor remains.
+ *
+ * Phase reduction without a rounding sequence or a float conversion: with
+ * magic = 1.5 * 2^(52 - K) the sum r = w (n - 1) + magic (ONE fused
+ * multiply-add, exact product) has ulp 2^-K, so the low word of r holds
+ * frac(w (n - 1)) in K-bit fixed point, modulo 2^32 -- for K = 32 the whole
+ * low word, valid while |w (n - 1)| < 2^19 turns; K = 24 reaches 2^27 turns
+ * at 3e-8 turns resolution (es_screen_fixed_bits). `shift` = 32 - K moves the
+ * fraction to the top of the word: a signed 32-bit fraction of a turn in
+ * [-0.5, 0.5), error <= 2^-(K+1) turns. */
+ES_SCR_HD int es_screen_fixed_bits(const double max_abs_turns)
+{
+    return max_abs_turns < 262144.0 ? 32 : 24;
+}
+
+ES_SCR_HD double es_screen_magic(const int fixed_bits)
+{
+    /* 1.5 * 2^(52 - K) */
+    return fixed_bits == 32 ? 1572864.0 : 402653184.0;
+}
+
+/* cos, sin of 2 pi frac(w_signed nm1), fp32 data */
+ES_SCR_HD void es_phasor_f32(const double nm1, const double w_signed,
+        const double magic, const int shift, float& re, float& im)
+{
+#if defined(__CUDA_ARCH__)
+    const double r = __fma_rn(w_signed, nm1, magic);
+    const int f = __double2loint(r) << shift;
+    /* 2 pi / 2^32; the special-function unit (abs. error ~4e-7) as before */
+    const float z = (float) f * 1.46291807926715968e-9f;
+    re = __cosf(z);
+    im = __sinf(z);
+#else
+    const double r = fma(w_signed, nm1, magic);
+    uint32_t hi, lo;
+    es_double_to_hilo(r, hi, lo);
+    const int32_t f = (int32_t) (lo << shift);
+    const float z = (float) f * 1.46291807926715968e-9f;
+    re = cosf(z);
+    im = sinf(z);
+#endif
+}
+
+/* n - 1 = -s / (sqrt(1 - s) + 1), s = l^2 + m^2 (kernels.cu:113-114), fp64 */
+ES_SCR_HD double es_screen_nm1(const uint32_t s2, const double pix2)
+{
+    const double sos = pix2 * (double) s2;
+    return (-sos) / (sqrt(1.0 - sos) + 1.0);
+}
+
 #endif

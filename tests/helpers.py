@@ -99,6 +99,10 @@ def check_parity_planes(case, eps, count, do_grid=True, do_degrid=True,
                          case["pixel_size"], eps, wstack)
     assert o.plan["grid_size"] == info["grid_size"]
     assert o.plan["num_total_w_grids"] == planes
+    # one lattice on both sides: an ulp of difference in max |w| (fp32) moves
+    # plane p by 6e-8 p planes, which alone exceeds the tolerance at p ~ 700
+    assert o.plan["w_scale"] == info["w_scale"] and \
+        o.plan["min_plane_w"] == info["min_plane_w"], (o.plan, info)
     if count is None or count >= planes:
         lo, hi = 0, planes
     else:

@@ -43,6 +43,31 @@ int main()
         if (e1 > max_sc) max_sc = e1;
         if (e2 > max_sc) max_sc = e2;
     }
-    printf("%.3e %.3e %.3e\n", max_ph, max_inv, max_sc);
+    // table form: n - 1 from fp64, phase reduced in fixed point (K = 32 / 24)
+    double max_fx[2] = {0.0, 0.0};
+    for (int kb = 0; kb < 2; ++kb)
+    {
+        const int bits = kb == 0 ? 32 : 24;
+        const double wmax = kb == 0 ? 2.5e5 : 6.0e7; // turns reach 2^18 / 2^26
+        for (int trial = 0; trial < 400000; ++trial)
+        {
+            const int iu = rand() % 8193, jv = rand() % 8193;
+            const double pix2 = 4.26e-5 * 4.26e-5;
+            const double nm1 = es_screen_nm1((uint32_t) (iu * iu + jv * jv), pix2);
+            const double w = (rand() / (double) RAND_MAX - 0.5) * 2.0 * wmax / 0.13;
+            if (fabs(w * nm1) >= (kb == 0 ? 262144.0 : 67108864.0)) continue;
+            if (es_screen_fixed_bits(fabs(w * nm1)) != bits && kb == 0) continue;
+            float re, im;
+            es_phasor_f32(nm1, w, es_screen_magic(bits), 32 - bits, re, im);
+            const long double t = (long double) w * (long double) nm1;
+            const long double fr = t - floorl(t);
+            const double ph = 2.0 * M_PI * (double) fr;
+            const double er = fabs(re - cos(ph)), ei = fabs(im - sin(ph));
+            if (er > max_fx[kb]) max_fx[kb] = er;
+            if (ei > max_fx[kb]) max_fx[kb] = ei;
+        }
+    }
+    printf("%.3e %.3e %.3e %.3e %.3e\n", max_ph, max_inv, max_sc, max_fx[0],
+            max_fx[1]);
     return 0;
 }

@@ -139,7 +139,7 @@ g.grid_uvw_es_fft(uvw, freq, vis, wgt, dirty)
 pred = np.zeros_like(vis)
 img = image.copy()
 g.ifft_grid_uvw_es(uvw, freq, pred, wgt, img)
-np.savez(sys.argv[3], dirty=dirty, pred=pred, img=img, lib=np.array(Lib.find_lib()))
+np.savez(sys.argv[3], dirty=dirty, pred=pred, img=img, lib=np.array(Lib.handle()._name))
 """
 
 
