@@ -412,10 +412,13 @@ ES_HD int es_padded(const EsFftPassArgs& pa, const int pos)
 #define ES_FFT_KIND_LAST 2   /* last stage of several */
 #define ES_FFT_KIND_ONLY 3   /* single-stage line */
 
-/* The pass functions are real device functions, one per (radix, kind), so
- * that each gets its own register allocation: inlined into one kernel the
- * ~60 of them share the worst case and spill (ptxas -v: 1 - 2.5 KB of spill
- * stores in the column kernels), -DES_FFT_PASS_INLINE restores that form. */
+/* In the generic kernels (any 11-smooth length, radix known at run time) the
+ * pass functions are real device functions, one per (radix, kind), so that
+ * each gets its own register allocation: inlined into one kernel the ~60 of
+ * them share the worst case and spill (ptxas -v: 1 - 2.5 KB of spill stores
+ * in the column kernels); -DES_FFT_PASS_INLINE restores that form. Kernels
+ * instantiated for a fixed stage list (EsFftSeq below) inline their 3 - 4
+ * passes. */
 #if defined(__CUDACC__) && !defined(ES_FFT_PASS_INLINE)
 #define ES_PASS_FN __device__ __noinline__
 #else
@@ -437,13 +440,10 @@ ES_HD int es_padded(const EsFftPassArgs& pa, const int pos)
  * The caller synchronises between passes. Returns in.any_bits(). */
 template<int R, int SGN, bool DIT, int KIND, typename T, typename T2,
         typename In, typename Out>
-ES_PASS_FN unsigned int es_line_pass_body(T2* x, const EsFftPassArgs pa,
+ES_HD unsigned int es_line_pass_body(T2* x, const EsFftPassArgs& pa,
         const T2* tw, const int32_t* bpos, const int lshift, const int pitch,
-        const int tid, const int nthreads, In in, Out out)
+        const int tid, const int nthreads, In& in, Out& out)
 {
-#if defined(__CUDA_ARCH__)
-    __builtin_assume(__isShared(x));
-#endif
     constexpr bool first_stage = (KIND == ES_FFT_KIND_FIRST ||
             KIND == ES_FFT_KIND_ONLY);
     constexpr bool last_stage = (KIND == ES_FFT_KIND_LAST ||
@@ -551,6 +551,21 @@ ES_PASS_FN unsigned int es_line_pass_body(T2* x, const EsFftPassArgs pa,
     return in.any_bits();
 }
 
+/* The same as a call (generic kernels): everything by value, x is known to
+ * be shared memory. */
+template<int R, int SGN, bool DIT, int KIND, typename T, typename T2,
+        typename In, typename Out>
+ES_PASS_FN unsigned int es_line_pass_call(T2* x, const EsFftPassArgs pa,
+        const T2* tw, const int32_t* bpos, const int lshift, const int pitch,
+        const int tid, const int nthreads, In in, Out out)
+{
+#if defined(__CUDA_ARCH__)
+    __builtin_assume(__isShared(x));
+#endif
+    return es_line_pass_body<R, SGN, DIT, KIND, T>(x, pa, tw, bpos, lshift,
+            pitch, tid, nthreads, in, out);
+}
+
 /* fp64 butterflies above radix 16 do not fit the register file and are
  * never planned (es_fft_line_plan): they are not instantiated. */
 #define ES_FFT_MAX_RADIX_DOUBLE 16
@@ -568,16 +583,16 @@ ES_HD unsigned int es_line_pass_r(T2* x, const EsFftPassArgs& pa,
         switch (kind)
         {
         case ES_FFT_KIND_FIRST:
-            return es_line_pass_body<R, SGN, DIT, ES_FFT_KIND_FIRST, T>(x, pa,
+            return es_line_pass_call<R, SGN, DIT, ES_FFT_KIND_FIRST, T>(x, pa,
                     tw, bpos, lshift, pitch, tid, nthreads, in, out);
         case ES_FFT_KIND_MIDDLE:
-            return es_line_pass_body<R, SGN, DIT, ES_FFT_KIND_MIDDLE, T>(x, pa,
+            return es_line_pass_call<R, SGN, DIT, ES_FFT_KIND_MIDDLE, T>(x, pa,
                     tw, bpos, lshift, pitch, tid, nthreads, in, out);
         case ES_FFT_KIND_LAST:
-            return es_line_pass_body<R, SGN, DIT, ES_FFT_KIND_LAST, T>(x, pa,
+            return es_line_pass_call<R, SGN, DIT, ES_FFT_KIND_LAST, T>(x, pa,
                     tw, bpos, lshift, pitch, tid, nthreads, in, out);
         default:
-            return es_line_pass_body<R, SGN, DIT, ES_FFT_KIND_ONLY, T>(x, pa,
+            return es_line_pass_call<R, SGN, DIT, ES_FFT_KIND_ONLY, T>(x, pa,
                     tw, bpos, lshift, pitch, tid, nthreads, in, out);
         }
     }
@@ -623,6 +638,93 @@ ES_HD void es_line_pass(T2* x, const EsFftLine& pl, const int step,
     }
 #undef ES_FFT_CASE
     in.merge_any(any);
+}
+
+/* ---- fixed stage lists ----
+ * A kernel instantiated for EsFftSeq<ID> (ID > 0) runs its passes with
+ * compile-time radices and kinds: no radix switch, a handful of passes inlined
+ * instead of ~60, registers allocated for exactly those (measured against the
+ * generic kernels on a B200: -13 % on the 24640-point lines, -7 % on 6160).
+ * The lists are the planner's (es_fft_line_plan) for the grid sizes of the
+ * BASELINE configurations; es_fft.cu picks a specialised kernel set when the
+ * plan's stage list equals one of them and the generic set otherwise. */
+template<int ID> struct EsFftSeq
+{
+    static constexpr int n = 0;
+    static constexpr int radix(int) { return 0; }
+};
+#define ES_FFT_SEQ(ID_, ...) \
+    template<> struct EsFftSeq<ID_> \
+    { \
+        static constexpr int n = sizeof((int[]) {__VA_ARGS__}) / sizeof(int); \
+        static constexpr int radix(int i) \
+        { \
+            constexpr int r[] = {__VA_ARGS__}; \
+            return r[i]; \
+        } \
+    };
+ES_FFT_SEQ(1, 28, 20, 11)     /* 6160: C2 */
+ES_FFT_SEQ(2, 16, 14, 10, 11) /* 24640: C4 */
+ES_FFT_SEQ(3, 32, 24, 15)     /* 11520: C5 */
+ES_FFT_SEQ(4, 15, 8, 8, 15)   /* 14400: C3 (fp64) */
+#define ES_FFT_NUM_SEQ 4
+/* (id, real type, is_double) of the kernel sets the Makefile builds (SEQ_IDS) */
+#define ES_FFT_SEQ_TABLE(X) X(1, float, 0) X(2, float, 0) X(3, float, 0) \
+    X(4, double, 1)
+
+template<int SEQ, int STAGE, int SGN, bool DIT, typename T, typename T2,
+        typename In, typename Out>
+ES_HD void es_line_pass_fixed(T2* x, const EsFftLine& pl, const T2* tw,
+        const int32_t* bpos, const int lshift, const int pitch, const int tid,
+        const int nthreads, In& in, Out& out)
+{
+    if constexpr (STAGE < EsFftSeq<SEQ>::n)
+    {
+        constexpr int NS = EsFftSeq<SEQ>::n;
+        constexpr int R = EsFftSeq<SEQ>::radix(STAGE);
+        constexpr int KIND = NS == 1 ? ES_FFT_KIND_ONLY :
+                STAGE == 0 ? ES_FFT_KIND_FIRST :
+                STAGE == NS - 1 ? ES_FFT_KIND_LAST : ES_FFT_KIND_MIDDLE;
+        EsFftPassArgs pa;
+        pa.st = pl.stage[STAGE];
+        pa.n = pl.n;
+        pa.pad = pl.pad;
+        pa.inv_stride0 = pl.inv_stride0;
+        in.merge_any(es_line_pass_body<R, SGN, DIT, KIND, T>(x, pa, tw, bpos,
+                lshift, pitch, tid, nthreads, in, out));
+    }
+}
+
+/* es_line_pass for a kernel instantiated with stage list SEQ (0: generic). */
+template<int SEQ, int SGN, bool DIT, typename T, typename T2, typename In,
+        typename Out>
+ES_HD void es_line_pass_seq(T2* x, const EsFftLine& pl, const int step,
+        const T2* tw, const int32_t* bpos, const int lshift, const int pitch,
+        const int tid, const int nthreads, In& in, Out& out)
+{
+    if constexpr (SEQ == 0)
+    {
+        es_line_pass<SGN, DIT, T>(x, pl, step, tw, bpos, lshift, pitch, tid,
+                nthreads, in, out);
+    }
+    else
+    {
+        const int stage = DIT ? EsFftSeq<SEQ>::n - 1 - step : step;
+        switch (stage)
+        {
+        case 0: es_line_pass_fixed<SEQ, 0, SGN, DIT, T>(x, pl, tw, bpos,
+                lshift, pitch, tid, nthreads, in, out); break;
+        case 1: es_line_pass_fixed<SEQ, 1, SGN, DIT, T>(x, pl, tw, bpos,
+                lshift, pitch, tid, nthreads, in, out); break;
+        case 2: es_line_pass_fixed<SEQ, 2, SGN, DIT, T>(x, pl, tw, bpos,
+                lshift, pitch, tid, nthreads, in, out); break;
+        case 3: es_line_pass_fixed<SEQ, 3, SGN, DIT, T>(x, pl, tw, bpos,
+                lshift, pitch, tid, nthreads, in, out); break;
+        case 4: es_line_pass_fixed<SEQ, 4, SGN, DIT, T>(x, pl, tw, bpos,
+                lshift, pitch, tid, nthreads, in, out); break;
+        default: break;
+        }
+    }
 }
 
 #endif

@@ -39,9 +39,14 @@ def test_c4_grid_size_24640_single_line_mode():
     print("C4 grid size", out, out2, info["num_total_w_grids"])
 
 
-def test_c5_grid_size_11520_eps_1e4():
+@pytest.mark.parametrize("generic", [False, True])
+def test_c5_grid_size_11520_eps_1e4(generic, monkeypatch):
     """BASELINE configs[4] shapes: 8192^2, eps = 1e-4 (W = 7, G = 11520: one
-    row per CTA in the row pass), wide field, 3 planes, both directions."""
+    row per CTA in the row pass), wide field, 3 planes, both directions; with
+    the kernel set built for this stage list (32, 24, 15) and with the generic
+    set (radix dispatch at run time) that every other length uses."""
+    if generic:
+        monkeypatch.setenv("SKA_SDP_FUNC_ES_FFT_GENERIC", "1")
     case = synth.wide_field(2000, 32, 8192, seed=44, single=True)
     out, info = check_parity_planes(case, 1e-4, 3)
     assert info["grid_size"] == 11520 and info["support"] == 7
