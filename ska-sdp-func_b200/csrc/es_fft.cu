@@ -50,7 +50,7 @@ int bundle_pitch(const EsFftLine* line, int lshift)
 }
 
 void make_cfg(const EsFftLine* line, size_t cplx, int lshift, int threads,
-        EsFftCfg* c)
+        int max_threads, EsFftCfg* c)
 {
     c->lshift = lshift;
     c->pitch = bundle_pitch(line, lshift);
@@ -70,11 +70,12 @@ void make_cfg(const EsFftLine* line, size_t cplx, int lshift, int threads,
     if (threads <= 0)
     {
         /* as many CTAs per SM as shared memory allows (at most 4), all of
-         * them together 512 threads of 128 registers */
+         * them together max_threads (512 threads of 128 registers; more
+         * where a specialised kernel set needs fewer registers) */
         int ctas = (int) ((size_t) ES_FFT_MAX_SMEM / (c->smem_bytes + 1024));
         if (ctas < 1) ctas = 1;
         if (ctas > 4) ctas = 4;
-        threads = ES_FFT_THREADS / ctas;
+        threads = ((max_threads / ctas) / 32) * 32;
         /* no more threads than butterflies of the narrowest pass */
         int min_bf = line->n;
         for (int i = 0; i < line->num_stages; ++i)
@@ -90,9 +91,9 @@ void make_cfg(const EsFftLine* line, size_t cplx, int lshift, int threads,
 } // namespace
 
 /* Kernel sets for fixed stage lists (es_fft_seq.cu, one object per list):
- * stage list and precision of set `id`, and its launch table (0 when the set
- * was not built into this library). */
-int es_fft_seq_info(int id, int32_t* radices, int* is_double);
+ * whether set `id` is for this precision and line plan, and its launch table
+ * (0 when the set was not built into this library). */
+int es_fft_seq_match(int id, const EsFftLine* line, int is_double);
 const EsFftOps* es_fft_seq_ops(int id);
 
 extern "C" {
@@ -134,6 +135,25 @@ int es_fft_create(int grid_size, int image_size, int is_double, EsFft** out)
     f->grid_size = grid_size;
     f->image_size = image_size;
     f->is_double = is_double;
+    /* kernel set: the one instantiated for exactly this stage list where
+     * there is one (SKA_SDP_FUNC_ES_FFT_GENERIC=1: tests of the generic set) */
+    f->ops = is_double ? EsFftLaunch<double, 0>::ops() :
+            EsFftLaunch<float, 0>::ops();
+    f->seq = 0;
+    if (!getenv("SKA_SDP_FUNC_ES_FFT_GENERIC"))
+    {
+        for (int id = 1; id <= ES_FFT_NUM_SEQ; ++id)
+        {
+            const EsFftOps* ops = es_fft_seq_match(id, &f->line, is_double) ?
+                    es_fft_seq_ops(id) : 0;
+            if (ops)
+            {
+                f->ops = ops;
+                f->seq = id;
+                break;
+            }
+        }
+    }
     const size_t cplx = is_double ? 16 : 8;
     /* experiments: SKA_SDP_FUNC_ES_FFT_CFG="rows_threads,cols_threads,cols_lshift"
      * default: bundles of 4 (fp64: 2) adjacent columns / 2 (fp64: 1) rows per CTA where they fit
@@ -145,13 +165,13 @@ int es_fft_create(int grid_size, int image_size, int is_double, EsFft** out)
             &e[3]) == 4;
     if (e[3] < 0 || e[3] > 2) e[3] = 0;
     for (int k = 0; k < 2; ++k)
-        if (e[k] < 0 || e[k] > ES_FFT_THREADS || (e[k] & 31)) e[k] = 0;
+        if (e[k] < 0 || e[k] > f->ops->max_threads || (e[k] & 31)) e[k] = 0;
     if (e[2] < 0 || e[2] > 2) e[2] = 0;
     /* rows of one CTA share a 64-row occupancy block and must tile the grid */
     int rshift = e[3];
     for (;; --rshift)
     {
-        make_cfg(&f->line, cplx, rshift, e[0], &f->rows);
+        make_cfg(&f->line, cplx, rshift, e[0], f->ops->max_threads, &f->rows);
         /* default: a row bundle only where two CTAs still fit on an SM (C5:
          * 2 rows of 11520 leave one 512-thread CTA: rows 1365 vs 1314 ms);
          * a bundle forced by the environment only has to fit */
@@ -163,11 +183,24 @@ int es_fft_create(int grid_size, int image_size, int is_double, EsFft** out)
     int lshift = e[2];
     for (;; --lshift)
     {
-        make_cfg(&f->line, cplx, lshift, e[1], &f->cols);
+        make_cfg(&f->line, cplx, lshift, e[1], f->ops->max_threads, &f->cols);
         if ((f->cols.smem_bytes <= ES_FFT_MAX_SMEM &&
                 image_size % (1 << lshift) == 0) || lshift == 0) break;
     }
     f->plane_elems = (int64_t) grid_size * image_size;
+    /* single-line column CTAs load their strip pieces as clusters of 2
+     * adjacent columns (whole / half sectors instead of quarters; clusters of
+     * 4 would leave 16 of the 148 SMs without a cluster slot).
+     * SKA_SDP_FUNC_ES_FFT_CLUSTER=0|2|4 overrides. */
+    f->cols_cluster = (f->cols.lshift == 0) ? 2 : 0;
+    const char* cenv = getenv("SKA_SDP_FUNC_ES_FFT_CLUSTER");
+    if (cenv && f->cols.lshift == 0)
+    {
+        const int v = atoi(cenv);
+        f->cols_cluster = (v == 2 || v == 4) ? v : 0;
+    }
+    if (f->cols_cluster && image_size % f->cols_cluster != 0)
+        f->cols_cluster = 0;
     if (f->rows.smem_bytes > ES_FFT_MAX_SMEM ||
             f->cols.smem_bytes > ES_FFT_MAX_SMEM)
     {
@@ -176,13 +209,14 @@ int es_fft_create(int grid_size, int image_size, int is_double, EsFft** out)
     }
     if (getenv("SKA_SDP_FUNC_ES_DEBUG"))
     {
-        fprintf(stderr, "es_fft: n=%d passes", grid_size);
+        fprintf(stderr, "es_fft: kernel set %d (0: generic); n=%d passes",
+                f->seq, grid_size);
         for (int k = 0; k < f->line.num_stages; ++k)
             fprintf(stderr, " %d", f->line.stage[k].radix);
         fprintf(stderr, "; pad %d; rows %d thr (%zu B), cols %d thr x %d lines "
-                "(%zu B)\n", f->line.pad, f->rows.threads,
+                "(%zu B), cluster %d\n", f->line.pad, f->rows.threads,
                 f->rows.smem_bytes, f->cols.threads, 1 << f->cols.lshift,
-                f->cols.smem_bytes);
+                f->cols.smem_bytes, f->cols_cluster);
     }
 
     const int nt = f->line.num_twiddles;
@@ -210,32 +244,6 @@ int es_fft_create(int grid_size, int image_size, int is_double, EsFft** out)
                 sizeof(int32_t) * (size_t) nb, cudaMemcpyHostToDevice);
     }
     free(tw); free(bpos); free(tw_t);
-    /* kernel set: the one instantiated for exactly this stage list where
-     * there is one (SKA_SDP_FUNC_ES_FFT_GENERIC=1: tests of the generic set) */
-    f->ops = is_double ? EsFftLaunch<double, 0>::ops() :
-            EsFftLaunch<float, 0>::ops();
-    f->seq = 0;
-    if (!getenv("SKA_SDP_FUNC_ES_FFT_GENERIC"))
-    {
-        for (int id = 1; id <= ES_FFT_NUM_SEQ; ++id)
-        {
-            int32_t radices[ES_FFT_MAX_STAGES];
-            int is_dbl = 0;
-            const int ns = es_fft_seq_info(id, radices, &is_dbl);
-            bool same = (ns == f->line.num_stages) && (is_dbl == is_double);
-            for (int i = 0; same && i < ns; ++i)
-                same = (radices[i] == f->line.stage[i].radix);
-            const EsFftOps* ops = same ? es_fft_seq_ops(id) : 0;
-            if (ops)
-            {
-                f->ops = ops;
-                f->seq = id;
-                break;
-            }
-        }
-    }
-    if (getenv("SKA_SDP_FUNC_ES_DEBUG"))
-        fprintf(stderr, "es_fft: kernel set %d (0: generic)\n", f->seq);
     if (!err) err = f->ops->prepare(ES_FFT_MAX_SMEM);
     if (!err)
     {

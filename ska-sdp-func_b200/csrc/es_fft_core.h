@@ -449,8 +449,10 @@ ES_HD unsigned int es_line_pass_body(T2* x, const EsFftPassArgs& pa,
     constexpr bool last_stage = (KIND == ES_FFT_KIND_LAST ||
             KIND == ES_FFT_KIND_ONLY);
     /* processing order: DIF stage 0 first, DIT last stage first */
-    constexpr bool from_in = DIT ? last_stage : first_stage;
-    constexpr bool to_out = DIT ? first_stage : last_stage;
+    /* In::preloaded: the line is already in x (natural order) */
+    constexpr bool from_in = !In::preloaded && (DIT ? last_stage : first_stage);
+    /* Out::in_place: the result stays in x (natural order) */
+    constexpr bool to_out = !Out::in_place && (DIT ? first_stage : last_stage);
     const EsFftStage& st = pa.st;
     const int per_line = pa.n / R;
     const int total = per_line << lshift;
@@ -648,48 +650,115 @@ ES_HD void es_line_pass(T2* x, const EsFftLine& pl, const int step,
  * The lists are the planner's (es_fft_line_plan) for the grid sizes of the
  * BASELINE configurations; es_fft.cu picks a specialised kernel set when the
  * plan's stage list equals one of them and the generic set otherwise. */
+#define ES_FFT_THREADS 512 /* CTA size limit of the generic kernels (128 registers each) */
 template<int ID> struct EsFftSeq
 {
     static constexpr int n = 0;
+    static constexpr int threads = ES_FFT_THREADS;
     static constexpr int radix(int) { return 0; }
 };
-#define ES_FFT_SEQ(ID_, ...) \
+/* THREADS_: CTA size limit of the set's kernels (ptxas keeps them within
+ * 65536 / THREADS_ registers): lines that fill shared memory run one CTA per
+ * SM, so every warp the register file can hold is one more to hide latency */
+#define ES_FFT_SEQ(ID_, THREADS_, ...) \
     template<> struct EsFftSeq<ID_> \
     { \
         static constexpr int n = sizeof((int[]) {__VA_ARGS__}) / sizeof(int); \
+        static constexpr int threads = THREADS_; \
         static constexpr int radix(int i) \
         { \
             constexpr int r[] = {__VA_ARGS__}; \
             return r[i]; \
         } \
     };
-ES_FFT_SEQ(1, 28, 20, 11)     /* 6160: C2 */
-ES_FFT_SEQ(2, 16, 14, 10, 11) /* 24640: C4 */
-ES_FFT_SEQ(3, 32, 24, 15)     /* 11520: C5 */
-ES_FFT_SEQ(4, 15, 8, 8, 15)   /* 14400: C3 (fp64) */
+ES_FFT_SEQ(1, 512, 28, 20, 11)     /* 6160: C2 */
+ES_FFT_SEQ(2, 640, 16, 14, 10, 11) /* 24640: C4, 96 registers */
+ES_FFT_SEQ(3, 512, 32, 24, 15)     /* 11520: C5 */
+ES_FFT_SEQ(4, 512, 15, 8, 8, 15)   /* 14400: C3 (fp64) */
 #define ES_FFT_NUM_SEQ 4
 /* (id, real type, is_double) of the kernel sets the Makefile builds (SEQ_IDS) */
 #define ES_FFT_SEQ_TABLE(X) X(1, float, 0) X(2, float, 0) X(3, float, 0) \
     X(4, double, 1)
 
+/* The line plan of a fixed stage list as compile-time constants: the same
+ * arithmetic as es_fft_line_plan (es_fft_plan.c) -- lengths, strides, twiddle
+ * table offsets, pad -- so that the passes of a specialised kernel address
+ * shared memory with immediate offsets instead of per-element integer
+ * arithmetic (profiles: LEA / IADD3 / IMAD / ISETP were ~30 % of the executed
+ * instructions of the column kernels). es_fft.cu checks it against the
+ * run-time plan before it selects a specialised kernel set. */
+struct EsFftSeqPlan
+{
+    int32_t n, num_stages, pad, num_twiddles;
+    int32_t radix[ES_FFT_MAX_STAGES], len[ES_FFT_MAX_STAGES];
+    int32_t stride[ES_FFT_MAX_STAGES];
+    int32_t tw_hi[ES_FFT_MAX_STAGES], tw_lo[ES_FFT_MAX_STAGES];
+};
+
+template<int ID> constexpr EsFftSeqPlan es_fft_seq_plan()
+{
+    EsFftSeqPlan p = {};
+    p.num_stages = EsFftSeq<ID>::n;
+    int32_t n = 1;
+    for (int i = 0; i < EsFftSeq<ID>::n; ++i) n *= EsFftSeq<ID>::radix(i);
+    p.n = n;
+    int32_t len = n, tw = 0;
+    for (int i = 0; i < EsFftSeq<ID>::n; ++i)
+    {
+        const int32_t r = EsFftSeq<ID>::radix(i);
+        p.radix[i] = r;
+        p.len[i] = len;
+        p.stride[i] = len / r;
+        p.tw_hi[i] = tw;
+        if (p.stride[i] > ES_FFT_TW_LO)
+            tw += (p.stride[i] + ES_FFT_TW_LO - 1) / ES_FFT_TW_LO;
+        p.tw_lo[i] = tw;
+        tw += p.stride[i] < ES_FFT_TW_LO ? p.stride[i] : ES_FFT_TW_LO;
+        len = p.stride[i];
+    }
+    p.num_twiddles = tw;
+    p.pad = (EsFftSeq<ID>::n > 1 && (p.stride[0] % 2 == 0)) ? 1 : 0;
+    return p;
+}
+
+/* true when the run-time plan is the compile-time one */
+template<int ID> inline bool es_fft_seq_matches(const EsFftLine& pl)
+{
+    constexpr EsFftSeqPlan p = es_fft_seq_plan<ID>();
+    bool same = pl.n == p.n && pl.num_stages == p.num_stages &&
+            pl.pad == p.pad && pl.num_twiddles == p.num_twiddles;
+    for (int i = 0; same && i < p.num_stages; ++i)
+        same = pl.stage[i].radix == p.radix[i] && pl.stage[i].len == p.len[i]
+                && pl.stage[i].stride == p.stride[i] &&
+                pl.stage[i].tw_hi == p.tw_hi[i] &&
+                pl.stage[i].tw_lo == p.tw_lo[i];
+    return same;
+}
+
 template<int SEQ, int STAGE, int SGN, bool DIT, typename T, typename T2,
         typename In, typename Out>
-ES_HD void es_line_pass_fixed(T2* x, const EsFftLine& pl, const T2* tw,
-        const int32_t* bpos, const int lshift, const int pitch, const int tid,
-        const int nthreads, In& in, Out& out)
+ES_HD void es_line_pass_fixed(T2* x, const T2* tw, const int32_t* bpos,
+        const int lshift, const int pitch, const int tid, const int nthreads,
+        In& in, Out& out)
 {
     if constexpr (STAGE < EsFftSeq<SEQ>::n)
     {
-        constexpr int NS = EsFftSeq<SEQ>::n;
-        constexpr int R = EsFftSeq<SEQ>::radix(STAGE);
+        constexpr EsFftSeqPlan P = es_fft_seq_plan<SEQ>();
+        constexpr int NS = P.num_stages;
+        constexpr int R = P.radix[STAGE];
         constexpr int KIND = NS == 1 ? ES_FFT_KIND_ONLY :
                 STAGE == 0 ? ES_FFT_KIND_FIRST :
                 STAGE == NS - 1 ? ES_FFT_KIND_LAST : ES_FFT_KIND_MIDDLE;
         EsFftPassArgs pa;
-        pa.st = pl.stage[STAGE];
-        pa.n = pl.n;
-        pa.pad = pl.pad;
-        pa.inv_stride0 = pl.inv_stride0;
+        pa.st.radix = R;
+        pa.st.len = P.len[STAGE];
+        pa.st.stride = P.stride[STAGE];
+        pa.st.tw_hi = P.tw_hi[STAGE];
+        pa.st.tw_lo = P.tw_lo[STAGE];
+        pa.st.inv_stride = 1.0f / (float) P.stride[STAGE];
+        pa.n = P.n;
+        pa.pad = P.pad;
+        pa.inv_stride0 = 1.0f / (float) P.stride[0];
         in.merge_any(es_line_pass_body<R, SGN, DIT, KIND, T>(x, pa, tw, bpos,
                 lshift, pitch, tid, nthreads, in, out));
     }
@@ -712,15 +781,15 @@ ES_HD void es_line_pass_seq(T2* x, const EsFftLine& pl, const int step,
         const int stage = DIT ? EsFftSeq<SEQ>::n - 1 - step : step;
         switch (stage)
         {
-        case 0: es_line_pass_fixed<SEQ, 0, SGN, DIT, T>(x, pl, tw, bpos,
+        case 0: es_line_pass_fixed<SEQ, 0, SGN, DIT, T>(x, tw, bpos,
                 lshift, pitch, tid, nthreads, in, out); break;
-        case 1: es_line_pass_fixed<SEQ, 1, SGN, DIT, T>(x, pl, tw, bpos,
+        case 1: es_line_pass_fixed<SEQ, 1, SGN, DIT, T>(x, tw, bpos,
                 lshift, pitch, tid, nthreads, in, out); break;
-        case 2: es_line_pass_fixed<SEQ, 2, SGN, DIT, T>(x, pl, tw, bpos,
+        case 2: es_line_pass_fixed<SEQ, 2, SGN, DIT, T>(x, tw, bpos,
                 lshift, pitch, tid, nthreads, in, out); break;
-        case 3: es_line_pass_fixed<SEQ, 3, SGN, DIT, T>(x, pl, tw, bpos,
+        case 3: es_line_pass_fixed<SEQ, 3, SGN, DIT, T>(x, tw, bpos,
                 lshift, pitch, tid, nthreads, in, out); break;
-        case 4: es_line_pass_fixed<SEQ, 4, SGN, DIT, T>(x, pl, tw, bpos,
+        case 4: es_line_pass_fixed<SEQ, 4, SGN, DIT, T>(x, tw, bpos,
                 lshift, pitch, tid, nthreads, in, out); break;
         default: break;
         }

@@ -8,18 +8,14 @@
 ES_FFT_SEQ_TABLE(X)
 #undef X
 
-template<int ID> static int seq_radices(int32_t* radices)
+/* 1 when kernel set `id` was built for this precision and exactly this line
+ * plan (stage list, strides, twiddle offsets, pad). */
+int es_fft_seq_match(int id, const EsFftLine* line, int is_double)
 {
-    for (int i = 0; i < EsFftSeq<ID>::n; ++i) radices[i] = EsFftSeq<ID>::radix(i);
-    return EsFftSeq<ID>::n;
-}
-
-int es_fft_seq_info(int id, int32_t* radices, int* is_double)
-{
-    *is_double = -1;
     switch (id)
     {
-#define X(ID, REAL, DBL) case ID: *is_double = DBL; return seq_radices<ID>(radices);
+#define X(ID, REAL, DBL) case ID: \
+        return (DBL == is_double) && es_fft_seq_matches<ID>(*line);
     ES_FFT_SEQ_TABLE(X)
 #undef X
     default: return 0;
