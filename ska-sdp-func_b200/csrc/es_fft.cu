@@ -188,19 +188,6 @@ int es_fft_create(int grid_size, int image_size, int is_double, EsFft** out)
                 image_size % (1 << lshift) == 0) || lshift == 0) break;
     }
     f->plane_elems = (int64_t) grid_size * image_size;
-    /* single-line column CTAs load their strip pieces as clusters of 2
-     * adjacent columns (whole / half sectors instead of quarters; clusters of
-     * 4 would leave 16 of the 148 SMs without a cluster slot).
-     * SKA_SDP_FUNC_ES_FFT_CLUSTER=0|2|4 overrides. */
-    f->cols_cluster = (f->cols.lshift == 0) ? 2 : 0;
-    const char* cenv = getenv("SKA_SDP_FUNC_ES_FFT_CLUSTER");
-    if (cenv && f->cols.lshift == 0)
-    {
-        const int v = atoi(cenv);
-        f->cols_cluster = (v == 2 || v == 4) ? v : 0;
-    }
-    if (f->cols_cluster && image_size % f->cols_cluster != 0)
-        f->cols_cluster = 0;
     if (f->rows.smem_bytes > ES_FFT_MAX_SMEM ||
             f->cols.smem_bytes > ES_FFT_MAX_SMEM)
     {
@@ -214,9 +201,9 @@ int es_fft_create(int grid_size, int image_size, int is_double, EsFft** out)
         for (int k = 0; k < f->line.num_stages; ++k)
             fprintf(stderr, " %d", f->line.stage[k].radix);
         fprintf(stderr, "; pad %d; rows %d thr (%zu B), cols %d thr x %d lines "
-                "(%zu B), cluster %d\n", f->line.pad, f->rows.threads,
+                "(%zu B)\n", f->line.pad, f->rows.threads,
                 f->rows.smem_bytes, f->cols.threads, 1 << f->cols.lshift,
-                f->cols.smem_bytes, f->cols_cluster);
+                f->cols.smem_bytes);
     }
 
     const int nt = f->line.num_twiddles;

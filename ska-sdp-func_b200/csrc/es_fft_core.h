@@ -449,10 +449,8 @@ ES_HD unsigned int es_line_pass_body(T2* x, const EsFftPassArgs& pa,
     constexpr bool last_stage = (KIND == ES_FFT_KIND_LAST ||
             KIND == ES_FFT_KIND_ONLY);
     /* processing order: DIF stage 0 first, DIT last stage first */
-    /* In::preloaded: the line is already in x (natural order) */
-    constexpr bool from_in = !In::preloaded && (DIT ? last_stage : first_stage);
-    /* Out::in_place: the result stays in x (natural order) */
-    constexpr bool to_out = !Out::in_place && (DIT ? first_stage : last_stage);
+    constexpr bool from_in = DIT ? last_stage : first_stage;
+    constexpr bool to_out = DIT ? first_stage : last_stage;
     const EsFftStage& st = pa.st;
     const int per_line = pa.n / R;
     const int total = per_line << lshift;
@@ -486,6 +484,13 @@ ES_HD unsigned int es_line_pass_body(T2* x, const EsFftPassArgs& pa,
             gidx = j; /* only used by stage 0 */
             gstride = st.stride;
         }
+        if constexpr (to_out && Out::skip_masked_butterflies)
+        {
+            /* sparse output (row pass that stores a few occupied tiles):
+             * nothing of this butterfly is kept */
+            if (!out.template any_stored<R>(out.cursor(line, gidx, gstride)))
+                continue;
+        }
         T2 v[R];
         if constexpr (from_in)
         {
@@ -493,12 +498,28 @@ ES_HD unsigned int es_line_pass_body(T2* x, const EsFftPassArgs& pa,
              * value is used */
             const typename In::Cursor c = in.cursor(line, gidx, gstride);
             typename In::Raw raw[R];
+            in.butterfly_begin();
 #pragma unroll
             for (int k = 0; k < R; ++k) raw[k] = in.fetch(c, k);
 #pragma unroll
             for (int k = 0; k + 1 < R; k += 2)
                 in.finish2(c, k, raw[k], raw[k + 1], v[k], v[k + 1]);
             if (R & 1) v[R - 1] = in.finish(c, R - 1, raw[R - 1]);
+            if constexpr (In::skip_zero_butterflies && !to_out)
+            {
+                /* sparse lines (row pass over a few occupied tiles): a
+                 * butterfly whose inputs are all zero stores zeros; runs of
+                 * occupied cells are contiguous in the butterfly index, so
+                 * warps mostly take one side */
+                if (!in.butterfly_nonzero())
+                {
+                    T2 zero;
+                    zero.x = 0; zero.y = 0;
+#pragma unroll
+                    for (int k = 0; k < R; ++k) xl[base + k * estride] = zero;
+                    continue;
+                }
+            }
         }
         else
         {

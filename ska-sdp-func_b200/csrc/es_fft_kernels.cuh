@@ -14,16 +14,14 @@
 #include <string.h>
 
 #include <cuda_runtime.h>
-#include <cooperative_groups.h>
 
 #include "es_device.h"
 #include "es_fft_core.h"
 #include "es_fft_plan.h"
 #include "es_screen.h"
 
-#define ES_FFT_CL_BATCH 4 /* cluster kernels: strip rows per thread in flight */
 #define ES_FFT_COL_GROUP 16 /* degridding column pass: bundles per CTA group */
-#define ES_FFT_MAX_SMEM (227 * 1024 - 1600) /* static: occupancy flags (512 B), tile-row list of the cluster kernels (1 KB), work item */
+#define ES_FFT_MAX_SMEM (227 * 1024 - 576) /* static: 512 B of occupancy flags + the work item */
 
 /* CTA shape of one kernel family. */
 struct EsFftCfg
@@ -51,7 +49,6 @@ struct EsFft
     uint32_t* d_row_work; /* [0] work items of the batch, [1] next item */
     int32_t row_list_cap; /* entries */
     int32_t rows_grid;    /* resident CTAs of the row kernels on this device */
-    int32_t cols_cluster; /* gridding column pass of single-line CTAs: cluster size (0: none) */
     /* w-screen (es_fft_set_screen): n - 1 per pixel of one image quadrant */
     double* d_nm1;        /* [image_size / 2 + 1][nm1_pitch] */
     int32_t nm1_pitch;
@@ -156,6 +153,17 @@ template<typename T2, bool WINDOW, bool ANY, bool MASK = false> struct LinearIn
     int k0, count;
     const uint8_t* bits;     /* MASK */
     unsigned int any;        /* ANY: becomes non-zero when a loaded value is */
+    unsigned int bf;         /* ANY: the same for the current butterfly */
+    /* ANY: butterflies of the first pass with all-zero inputs are skipped */
+    static constexpr bool skip_zero_butterflies = ANY;
+    __device__ __forceinline__ void butterfly_begin()
+    {
+        if (ANY) { any |= bf; bf = 0u; }
+    }
+    __device__ __forceinline__ bool butterfly_nonzero()
+    {
+        return bf != 0u;
+    }
     __device__ __forceinline__ Cursor cursor(int line, int idx0, int gs) const
     {
         Cursor c;
@@ -166,8 +174,7 @@ template<typename T2, bool WINDOW, bool ANY, bool MASK = false> struct LinearIn
         return c;
     }
     typedef T2 Raw;
-    static constexpr bool preloaded = false;
-    __device__ __forceinline__ unsigned int any_bits() const { return any; }
+    __device__ __forceinline__ unsigned int any_bits() const { return any | bf; }
     __device__ __forceinline__ void merge_any(unsigned int a) { any |= a; }
     __device__ __forceinline__ T2 finish(const Cursor&, int, const T2 v) const
     {
@@ -186,12 +193,13 @@ template<typename T2, bool WINDOW, bool ANY, bool MASK = false> struct LinearIn
         if ((!WINDOW || (unsigned) (c.r0 + k * c.gs) < (unsigned) count) &&
                 (!MASK || occ_bit(bits, c.r0 + k * c.gs)))
             v = c.p[k * c.step];
-        if (ANY) any |= nonzero_bits(v); /* -0.0 counts: it only costs an FFT */
+        if (ANY) bf |= nonzero_bits(v); /* -0.0 counts: it only costs an FFT */
         return v;
     }
 };
 
-template<typename T2, bool WINDOW, bool MASK = false> struct LinearOut
+template<typename T2, bool WINDOW, bool MASK = false, bool SKIP = false>
+struct LinearOut
 {
     struct Cursor
     {
@@ -218,9 +226,23 @@ template<typename T2, bool WINDOW, bool MASK = false> struct LinearOut
                 (!MASK || occ_bit(bits, c.r0 + k * c.gs)))
             c.p[k * c.step] = v;
     }
+    /* SKIP (with MASK): butterflies of the last pass none of whose outputs
+     * is stored are skipped (row pass onto a few occupied tiles) */
+    static constexpr bool skip_masked_butterflies = MASK && SKIP;
+    int sparse;              /* SKIP: worth testing (few occupied blocks) */
+    template<int R>
+    __device__ __forceinline__ bool any_stored(const Cursor& c) const
+    {
+        if (!sparse) return true;
+        bool on = false;
+#pragma unroll
+        for (int k = 0; k < R; ++k)
+            on = on || ((!WINDOW || (unsigned) (c.r0 + k * c.gs) <
+                    (unsigned) count) && occ_bit(bits, c.r0 + k * c.gs));
+        return on;
+    }
     /* nothing to prefetch */
     struct Pre {};
-    static constexpr bool in_place = false;
     __device__ __forceinline__ Pre prefetch(const Cursor&, int) const
     {
         return Pre();
@@ -236,56 +258,6 @@ template<typename T2, bool WINDOW, bool MASK = false> struct LinearOut
         store(c, k, v0);
         store(c, k + 1, v1);
     }
-};
-
-/* Input functor of a line that is already in shared memory (natural order,
- * padded): the first pass works in place like the others. */
-template<typename T2> struct PreloadedIn
-{
-    struct Cursor {};
-    typedef T2 Raw;
-    static constexpr bool preloaded = true;
-    __device__ __forceinline__ unsigned int any_bits() const { return 0u; }
-    __device__ __forceinline__ void merge_any(unsigned int) {}
-    __device__ __forceinline__ Cursor cursor(int, int, int) const
-    {
-        return Cursor();
-    }
-    __device__ __forceinline__ T2 fetch(const Cursor&, int) const
-    {
-        T2 v; v.x = 0; v.y = 0; return v;
-    }
-    __device__ __forceinline__ T2 finish(const Cursor&, int, const T2 v) const
-    {
-        return v;
-    }
-    __device__ __forceinline__ void finish2(const Cursor&, int, const T2 r0,
-            const T2 r1, T2& v0, T2& v1) const
-    {
-        v0 = r0;
-        v1 = r1;
-    }
-};
-
-/* Output functor of a line that stays in shared memory (natural order,
- * padded): the last pass works in place like the others. */
-template<typename T2> struct InPlaceOut
-{
-    struct Cursor {};
-    struct Pre {};
-    static constexpr bool in_place = true;
-    __device__ __forceinline__ Cursor cursor(int, int, int) const
-    {
-        return Cursor();
-    }
-    __device__ __forceinline__ Pre prefetch(const Cursor&, int) const
-    {
-        return Pre();
-    }
-    __device__ __forceinline__ void store1(const Cursor&, int, const T2,
-            const Pre) const {}
-    __device__ __forceinline__ void store2(const Cursor&, int, const T2,
-            const T2, const Pre, const Pre) const {}
 };
 
 /* gridding pass 2 output: w-screen phasor and sum into imageT
@@ -313,9 +285,9 @@ template<typename T, typename T2> struct ScreenOut
         c.p = image_t + (ptrdiff_t) line * n + c.iu0;
         return c;
     }
+    static constexpr bool skip_masked_butterflies = false;
     /* n - 1 of output k, loaded before the butterfly arithmetic */
     typedef double Pre;
-    static constexpr bool in_place = false;
     __device__ __forceinline__ Pre prefetch(const Cursor& c, int k) const
     {
         const int iu = c.iu0 + k * c.gs;
@@ -388,7 +360,9 @@ template<typename T, typename T2> struct ScreenIn
         T d;
         double nm1;
     };
-    static constexpr bool preloaded = false;
+    static constexpr bool skip_zero_butterflies = false;
+    __device__ __forceinline__ void butterfly_begin() const {}
+    __device__ __forceinline__ bool butterfly_nonzero() const { return true; }
     __device__ __forceinline__ unsigned int any_bits() const { return 0u; }
     __device__ __forceinline__ void merge_any(unsigned int) {}
     /* the image value (0 outside the image) and n - 1; no arithmetic yet */
@@ -605,6 +579,7 @@ __global__ void __launch_bounds__(EsFftSeq<SEQ>::threads, 1) es_fft_grid_rows_ke
         in.k0 = 0;
         in.count = gsz;
         in.any = 0u;
+        in.bf = 0u;
         LinearOut<T2, true> out;
         out.base = strip + (size_t) q * lay.plane_elems + (size_t) u * n;
         out.estride = 1;
@@ -669,6 +644,7 @@ es_fft_grid_cols_screen_kernel(const EsFftLine pl,
     in.k0 = 0;
     in.count = gsz;
     in.any = 0u;
+    in.bf = 0u;
     ScreenOut<T, T2> out;
     out.image_t = image_t + (size_t) col0 * n + n / 2;
     out.n = n;
@@ -696,175 +672,6 @@ es_fft_grid_cols_screen_kernel(const EsFftLine pl,
                     out);
         }
     }
-}
-
-/* Tile rows of a column line for one CTA of a cluster, from the occupancy
- * bytes: rows[0 .. count[0]) = occupied tile rows with tr % cs == rank (this
- * CTA's share of the cooperative loads / stores), rows[ES_FFT_MAX_TILE_ROWS -
- * count[1] ..) = the unoccupied ones (zero-filled locally). One warp builds
- * the list; contains a barrier. */
-#define ES_FFT_MAX_TILE_ROWS (ES_FFT_OCC_WORDS * 32)
-__device__ __forceinline__ void cluster_row_list(const uint8_t* s_bits,
-        const int ntile, const int cs, const int rank, uint16_t* rows,
-        int* count)
-{
-    if (threadIdx.x < 32)
-    {
-        const int lane = threadIdx.x;
-        int n_on = 0, n_off = 0;
-        for (int t0 = 0; t0 < ntile; t0 += 32)
-        {
-            const int tr = t0 + lane;
-            const bool valid = tr < ntile;
-            const bool on = valid && s_bits[tr] != 0;
-            const bool mine = on && (tr % cs) == rank;
-            const bool off = valid && !on;
-            const unsigned m_on = __ballot_sync(0xffffffffu, mine);
-            const unsigned m_off = __ballot_sync(0xffffffffu, off);
-            const unsigned below = (1u << lane) - 1u;
-            if (mine) rows[n_on + __popc(m_on & below)] = (uint16_t) tr;
-            if (off) rows[ES_FFT_MAX_TILE_ROWS - 1 - n_off -
-                    __popc(m_off & below)] = (uint16_t) tr;
-            n_on += __popc(m_on);
-            n_off += __popc(m_off);
-        }
-        if (lane == 0) { count[0] = n_on; count[1] = n_off; }
-    }
-    __syncthreads();
-}
-
-/* The same for lines that fill shared memory (one column per CTA), as a
- * thread-block cluster of CS CTAs on CS adjacent columns. A lone CTA reads its
- * column as 8- (fp32) or 16-byte pieces one strip row apart: every thread of
- * a load instruction touches its own 32-byte sector, a quarter (half) of
- * which it uses, and the load / store unit spends one wavefront per thread
- * (ncu, C4: l1tex data-pipe wavefronts 59 % of peak over the whole kernel,
- * i.e. saturated during the first pass). Here CTA r of the cluster loads the
- * CS x 8 (16) byte pieces of the strip rows of every CS-th occupied tile row
- * -- whole sectors for CS x sizeof(T2) = 32 -- and hands column c of each to
- * CTA c through distributed shared memory, coalesced; unoccupied tile rows
- * are zero-filled locally, and the first radix pass runs in place from shared
- * memory like the others. */
-template<typename T, int SEQ, int CS>
-__global__ void __cluster_dims__(CS, 1, 1)
-__launch_bounds__(EsFftSeq<SEQ>::threads, 1)
-es_fft_grid_cols_cluster_kernel(const EsFftLine pl,
-        const typename Cx<T>::T2* __restrict__ tw_g,
-        const int32_t* __restrict__ bpos, const EsGeom g,
-        const typename Cx<T>::T2* __restrict__ strip, const int first_plane,
-        const int nplanes, T* __restrict__ image_t,
-        const uint32_t* __restrict__ occ, const EsFftLayout lay)
-{
-    namespace cg = cooperative_groups;
-    typedef typename Cx<T>::T2 T2;
-    extern __shared__ __align__(16) unsigned char es_fft_smem[];
-    __shared__ uint8_t s_bits[ES_FFT_OCC_BYTES];
-    __shared__ uint16_t s_rows[ES_FFT_MAX_TILE_ROWS];
-    __shared__ int s_count[2];
-    cg::cluster_group cluster = cg::this_cluster();
-    const int rank = (int) cluster.block_rank();
-    T2* x = (T2*) es_fft_smem;
-    const T2* tw = lay.cols_twg ? tw_g : x + (size_t) lay.cols_pitch;
-    const int gsz = pl.n, n = g.image_size;
-    const int col = (int) blockIdx.x;           /* this CTA's column */
-    const int col0 = col - rank;                /* first column of the cluster */
-    T2* peer[CS];
-#pragma unroll
-    for (int c = 0; c < CS; ++c)
-        peer[c] = (c == rank) ? x : cluster.map_shared_rank(x, c);
-    EsFftPassArgs pad_args;                     /* es_padded */
-    pad_args.pad = pl.pad;
-    pad_args.inv_stride0 = pl.inv_stride0;
-    PreloadedIn<T2> in;
-    ScreenOut<T, T2> out;
-    out.image_t = image_t + (size_t) col * n + n / 2;
-    out.n = n;
-    out.half = n / 2;
-    out.gh = gsz / 2;
-    out.jv0 = col - n / 2;
-    out.wstack = g.do_wstacking;
-    out.tb = lay.screen;
-    load_twiddles(tw, tw_g, pl.num_twiddles);
-    for (int q = 0; q < nplanes; ++q)
-    {
-        /* every CTA of the cluster is done with the previous plane's line
-         * (peers write into it next); also: twiddles loaded */
-        cluster.sync();
-        /* rows of unoccupied tile rows were not stored; an empty plane adds
-         * nothing (the same decision in every CTA of the cluster) */
-        if (!occ_fetch(s_bits, occ_plane(occ, lay, q) +
-                lay.ntile * lay.occ_nw, lay.occ_nw)) continue;
-        const T2* src = strip + (size_t) q * lay.plane_elems + col0;
-        cluster_row_list(s_bits, lay.ntile, CS, rank, s_rows, s_count);
-        /* zero fill of the unoccupied tile rows (local) */
-        {
-            T2 zero;
-            zero.x = 0; zero.y = 0;
-            const int rows_off = s_count[1] << 6;
-            for (int r = threadIdx.x; r < rows_off; r += blockDim.x)
-            {
-                const int u = ((int) s_rows[ES_FFT_MAX_TILE_ROWS - 1 -
-                        (r >> 6)] << 6) + (r & 63);
-                if (u < gsz) x[es_padded(pad_args, u)] = zero;
-            }
-        }
-        /* this CTA's share of the occupied tile rows: CS adjacent columns of
-         * strip row u are CS x sizeof(T2) bytes, aligned (n and col0 are
-         * multiples of CS); ES_FFT_CL_BATCH rows per thread in flight */
-        const int rows_on = s_count[0] << 6;
-        for (int r0 = 0; r0 < rows_on; r0 += ES_FFT_CL_BATCH * (int) blockDim.x)
-        {
-            T2 v[ES_FFT_CL_BATCH][CS];
-            int pos[ES_FFT_CL_BATCH];
-#pragma unroll
-            for (int i = 0; i < ES_FFT_CL_BATCH; ++i)
-            {
-                const int r = r0 + i * (int) blockDim.x + (int) threadIdx.x;
-                pos[i] = -1;
-                if (r >= rows_on) continue;
-                const int u = ((int) s_rows[r >> 6] << 6) + (r & 63);
-                if (u >= gsz) continue;
-                pos[i] = es_padded(pad_args, u);
-                const T2* p = src + (size_t) u * n;
-                if (sizeof(T2) * CS == 16)
-                {
-                    const float4 w = *reinterpret_cast<const float4*>(p);
-                    memcpy(v[i], &w, 16);
-                }
-                else if (sizeof(T2) * CS == 32)
-                {
-                    const float4 w0 = reinterpret_cast<const float4*>(p)[0];
-                    const float4 w1 = reinterpret_cast<const float4*>(p)[1];
-                    memcpy(v[i], &w0, 16);
-                    memcpy((char*) v[i] + 16, &w1, 16);
-                }
-                else
-                {
-#pragma unroll
-                    for (int c = 0; c < CS; ++c) v[i][c] = p[c];
-                }
-            }
-#pragma unroll
-            for (int i = 0; i < ES_FFT_CL_BATCH; ++i)
-            {
-                if (pos[i] < 0) continue;
-#pragma unroll
-                for (int c = 0; c < CS; ++c) peer[c][pos[i]] = v[i][c];
-            }
-        }
-        /* the line is complete in every CTA */
-        cluster.sync();
-        out.w = -((double) (first_plane + q) * g.inv_w_scale + g.min_plane_w);
-        for (int step = 0; step < pl.num_stages; ++step)
-        {
-            if (step > 0) __syncthreads();
-            es_line_pass_seq<SEQ, 1, false, T>(x, pl, step, tw, bpos, 0,
-                    lay.cols_pitch, (int) threadIdx.x, (int) blockDim.x, in,
-                    out);
-        }
-    }
-    /* no CTA leaves while a peer may still address its shared memory */
-    cluster.sync();
 }
 
 /* ---------------------------------------------------- degridding pass 1 */
@@ -921,120 +728,6 @@ __global__ void __launch_bounds__(EsFftSeq<SEQ>::threads, 1) es_fft_degrid_cols_
             lay.lshift, lay.cols_pitch, in, out);
 }
 
-/* The same for lines that fill shared memory, as a cluster of CS CTAs on CS
- * adjacent columns of one plane (see es_fft_grid_cols_cluster_kernel): the
- * last pass leaves the transformed column in shared memory, then CTA r
- * collects, for the strip rows of every CS-th stored tile row, the CS columns
- * from its peers through distributed shared memory and stores them as one
- * CS x sizeof(T2)-byte piece -- whole 32-byte sectors for fp32 x 4 and
- * fp64 x 2 -- instead of every CTA storing 8 (16) bytes per row. */
-template<typename T, int SEQ, int CS>
-__global__ void __cluster_dims__(CS, 1, 1)
-__launch_bounds__(EsFftSeq<SEQ>::threads, 1)
-es_fft_degrid_cols_cluster_kernel(const EsFftLine pl,
-        const typename Cx<T>::T2* __restrict__ tw_g,
-        const int32_t* __restrict__ bpos, const EsGeom g,
-        const T* __restrict__ image_t, const int first_plane,
-        const int nplanes, typename Cx<T>::T2* __restrict__ strip,
-        const uint32_t* __restrict__ occ, const EsFftLayout lay)
-{
-    namespace cg = cooperative_groups;
-    typedef typename Cx<T>::T2 T2;
-    extern __shared__ __align__(16) unsigned char es_fft_smem[];
-    __shared__ uint8_t s_bits[ES_FFT_OCC_BYTES];
-    __shared__ uint16_t s_rows[ES_FFT_MAX_TILE_ROWS];
-    __shared__ int s_count[2];
-    cg::cluster_group cluster = cg::this_cluster();
-    const int rank = (int) cluster.block_rank();
-    T2* x = (T2*) es_fft_smem;
-    const T2* tw = lay.cols_twg ? tw_g : x + (size_t) lay.cols_pitch;
-    const int gsz = pl.n, n = g.image_size;
-    /* CTA order as in es_fft_degrid_cols_kernel; the CTAs of a cluster are
-     * adjacent columns of one group and plane (ES_FFT_COL_GROUP and n are
-     * multiples of CS), so the early exits below are taken by whole clusters */
-    const int grp = blockIdx.x / (ES_FFT_COL_GROUP * nplanes);
-    const int rem = blockIdx.x - grp * (ES_FFT_COL_GROUP * nplanes);
-    const int q = rem / ES_FFT_COL_GROUP;
-    const int col = grp * ES_FFT_COL_GROUP + (rem - q * ES_FFT_COL_GROUP);
-    if (col >= n) return;
-    const int col0 = col - rank;
-    if (!occ_fetch(s_bits, occ_plane(occ, lay, q) + lay.ntile * lay.occ_nw,
-            lay.occ_nw)) return;
-    ScreenIn<T, T2> in;
-    in.image_t = image_t + (size_t) col * n + n / 2;
-    in.n = n;
-    in.half = n / 2;
-    in.gh = gsz / 2;
-    in.jv0 = col - n / 2;
-    in.wstack = g.do_wstacking;
-    in.tb = lay.screen;
-    in.w = (double) (first_plane + q) * g.inv_w_scale + g.min_plane_w;
-    InPlaceOut<T2> out;
-    load_twiddles(tw, tw_g, pl.num_twiddles);
-    __syncthreads();
-    fft_all_passes<SEQ, -1, true, T>(x, pl, tw, bpos, 0, lay.cols_pitch, in,
-            out);
-    /* every column of the cluster is complete in its CTA */
-    cluster.sync();
-    const T2* peer[CS];
-#pragma unroll
-    for (int c = 0; c < CS; ++c)
-        peer[c] = (c == rank) ? x : cluster.map_shared_rank(x, c);
-    EsFftPassArgs pad_args;
-    pad_args.pad = pl.pad;
-    pad_args.inv_stride0 = pl.inv_stride0;
-    T2* dst = strip + (size_t) q * lay.plane_elems + col0;
-    /* only the tile rows the gather reads are stored: this CTA's share,
-     * ES_FFT_CL_BATCH rows per thread in flight */
-    cluster_row_list(s_bits, lay.ntile, CS, rank, s_rows, s_count);
-    const int rows_on = s_count[0] << 6;
-    for (int r0 = 0; r0 < rows_on; r0 += ES_FFT_CL_BATCH * (int) blockDim.x)
-    {
-        T2 v[ES_FFT_CL_BATCH][CS];
-        int row[ES_FFT_CL_BATCH];
-#pragma unroll
-        for (int i = 0; i < ES_FFT_CL_BATCH; ++i)
-        {
-            const int r = r0 + i * (int) blockDim.x + (int) threadIdx.x;
-            row[i] = -1;
-            if (r >= rows_on) continue;
-            const int u = ((int) s_rows[r >> 6] << 6) + (r & 63);
-            if (u >= gsz) continue;
-            row[i] = u;
-            const int pos = es_padded(pad_args, u);
-#pragma unroll
-            for (int c = 0; c < CS; ++c) v[i][c] = peer[c][pos];
-        }
-#pragma unroll
-        for (int i = 0; i < ES_FFT_CL_BATCH; ++i)
-        {
-            if (row[i] < 0) continue;
-            T2* p = dst + (size_t) row[i] * n;
-            if (sizeof(T2) * CS == 16)
-            {
-                float4 w;
-                memcpy(&w, v[i], 16);
-                *reinterpret_cast<float4*>(p) = w;
-            }
-            else if (sizeof(T2) * CS == 32)
-            {
-                float4 w0, w1;
-                memcpy(&w0, v[i], 16);
-                memcpy(&w1, (const char*) v[i] + 16, 16);
-                reinterpret_cast<float4*>(p)[0] = w0;
-                reinterpret_cast<float4*>(p)[1] = w1;
-            }
-            else
-            {
-#pragma unroll
-                for (int c = 0; c < CS; ++c) p[c] = v[i][c];
-            }
-        }
-    }
-    /* no CTA leaves while a peer may still read its shared memory */
-    cluster.sync();
-}
-
 /* ---------------------------------------------------- degridding pass 2 */
 
 template<typename T, int SEQ>
@@ -1063,6 +756,15 @@ __global__ void __launch_bounds__(EsFftSeq<SEQ>::threads, 1) es_fft_degrid_rows_
         if (u >= gsz) continue;
         occ_fetch(s_bits, occ_plane(occ, lay, q) + (u >> 6) * lay.occ_nw,
                 lay.occ_nw);
+        /* occupied tiles of this tile row: the output test of the last pass
+         * pays off when they are few (SKA-Low: 1-3 of 385; dense coverage
+         * would only pay for the test) */
+        int occupied = 0;
+        for (int t0 = 0; t0 < lay.ntile; t0 += (int) blockDim.x)
+        {
+            const int t = t0 + (int) threadIdx.x;
+            occupied += __syncthreads_count(t < lay.ntile && s_bits[t] != 0);
+        }
         LinearIn<T2, true, false> in;
         in.base = strip + (size_t) q * lay.plane_elems + (size_t) u * n;
         in.estride = 1;
@@ -1070,7 +772,9 @@ __global__ void __launch_bounds__(EsFftSeq<SEQ>::threads, 1) es_fft_degrid_rows_
         in.k0 = gsz / 2 - n / 2;
         in.count = n;
         in.any = 0u;
-        LinearOut<T2, false, true> out;
+        in.bf = 0u;
+        LinearOut<T2, false, true, true> out;
+        out.sparse = (occupied * 8 < lay.ntile);
         out.bits = s_bits;
         out.base = planes + ((size_t) q * gsz + u) * gsz;
         out.estride = 1;
@@ -1230,10 +934,6 @@ template<typename T, int SEQ> struct EsFftLaunch
     {
         int err = fft_set_smem(es_fft_grid_rows_kernel<T, SEQ>, max_smem);
         if (!err) err = fft_set_smem(es_fft_grid_cols_screen_kernel<T, SEQ>, max_smem);
-        if (!err) err = fft_set_smem(es_fft_grid_cols_cluster_kernel<T, SEQ, 2>, max_smem);
-        if (!err) err = fft_set_smem(es_fft_grid_cols_cluster_kernel<T, SEQ, 4>, max_smem);
-        if (!err) err = fft_set_smem(es_fft_degrid_cols_cluster_kernel<T, SEQ, 2>, max_smem);
-        if (!err) err = fft_set_smem(es_fft_degrid_cols_cluster_kernel<T, SEQ, 4>, max_smem);
         if (!err) err = fft_set_smem(es_fft_degrid_cols_kernel<T, SEQ>, max_smem);
         if (!err) err = fft_set_smem(es_fft_degrid_rows_kernel<T, SEQ>, max_smem);
         return err;
@@ -1266,20 +966,7 @@ template<typename T, int SEQ> struct EsFftLaunch
     {
         const EsFftLayout lay = fft_layout(f);
         const EsFftCfg& c = f->cols;
-        if (f->cols_cluster == 2)
-            es_fft_grid_cols_cluster_kernel<T, SEQ, 2><<<
-                    (unsigned) f->image_size, c.threads, c.smem_bytes, s>>>(
-                    f->line, (const T2*) f->d_tw, f->d_bpos, *g,
-                    (const T2*) strip, first_plane, nplanes, (T*) image_t, occ,
-                    lay);
-        else if (f->cols_cluster == 4)
-            es_fft_grid_cols_cluster_kernel<T, SEQ, 4><<<
-                    (unsigned) f->image_size, c.threads, c.smem_bytes, s>>>(
-                    f->line, (const T2*) f->d_tw, f->d_bpos, *g,
-                    (const T2*) strip, first_plane, nplanes, (T*) image_t, occ,
-                    lay);
-        else
-            es_fft_grid_cols_screen_kernel<T, SEQ><<<
+        es_fft_grid_cols_screen_kernel<T, SEQ><<<
                     (unsigned) (f->image_size >> c.lshift), c.threads,
                     c.smem_bytes, s>>>(f->line, (const T2*) f->d_tw, f->d_bpos,
                     *g, (const T2*) strip, first_plane, nplanes, (T*) image_t,
@@ -1296,18 +983,7 @@ template<typename T, int SEQ> struct EsFftLaunch
         const int nbundles = f->image_size >> c.lshift;
         const int groups = (nbundles + ES_FFT_COL_GROUP - 1) / ES_FFT_COL_GROUP;
         const unsigned ctas = (unsigned) (groups * ES_FFT_COL_GROUP * nplanes);
-        if (f->cols_cluster == 2)
-            es_fft_degrid_cols_cluster_kernel<T, SEQ, 2><<<ctas, c.threads,
-                    c.smem_bytes, s>>>(f->line, (const T2*) f->d_tw, f->d_bpos,
-                    *g, (const T*) image_t, first_plane, nplanes, (T2*) strip,
-                    occ, lay);
-        else if (f->cols_cluster == 4)
-            es_fft_degrid_cols_cluster_kernel<T, SEQ, 4><<<ctas, c.threads,
-                    c.smem_bytes, s>>>(f->line, (const T2*) f->d_tw, f->d_bpos,
-                    *g, (const T*) image_t, first_plane, nplanes, (T2*) strip,
-                    occ, lay);
-        else
-            es_fft_degrid_cols_kernel<T, SEQ><<<ctas, c.threads,
+        es_fft_degrid_cols_kernel<T, SEQ><<<ctas, c.threads,
                     c.smem_bytes, s>>>(f->line, (const T2*) f->d_tw, f->d_bpos,
                     *g, (const T*) image_t, first_plane, nplanes, (T2*) strip,
                     occ, lay);

@@ -21,7 +21,9 @@ template<typename T> struct InF
     typedef C2<T> Raw;
     C2<T> fetch(const Cursor& c, int k) const { return c.p[k * c.gs]; }
     C2<T> finish(const Cursor&, int, const C2<T> v) const { return v; }
-    static constexpr bool preloaded = false;
+    static constexpr bool skip_zero_butterflies = false;
+    void butterfly_begin() const {}
+    bool butterfly_nonzero() const { return true; }
     unsigned int any_bits() const { return 0u; }
     void merge_any(unsigned int) {}
     void finish2(const Cursor&, int, C2<T> r0, C2<T> r1, C2<T>& v0, C2<T>& v1) const
@@ -37,7 +39,7 @@ template<typename T> struct OutF
     Cursor cursor(int line, int idx0, int gs) const { return Cursor{dst + (size_t) line * n + idx0, gs}; }
     void store(const Cursor& c, int k, C2<T> v) const { c.p[k * c.gs] = v; }
     struct Pre {};
-    static constexpr bool in_place = false;
+    static constexpr bool skip_masked_butterflies = false;
     Pre prefetch(const Cursor&, int) const { return Pre(); }
     void store1(const Cursor& c, int k, C2<T> v, Pre) const { store(c, k, v); }
     void store2(const Cursor& c, int k, C2<T> v0, C2<T> v1, Pre, Pre) const
