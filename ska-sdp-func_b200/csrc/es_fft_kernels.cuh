@@ -756,9 +756,7 @@ __global__ void __launch_bounds__(EsFftSeq<SEQ>::threads, 1) es_fft_degrid_rows_
         if (u >= gsz) continue;
         occ_fetch(s_bits, occ_plane(occ, lay, q) + (u >> 6) * lay.occ_nw,
                 lay.occ_nw);
-        /* occupied tiles of this tile row: the output test of the last pass
-         * pays off when they are few (SKA-Low: 1-3 of 385; dense coverage
-         * would only pay for the test) */
+        /* occupied tiles of this tile row */
         int occupied = 0;
         for (int t0 = 0; t0 < lay.ntile; t0 += (int) blockDim.x)
         {
@@ -774,7 +772,11 @@ __global__ void __launch_bounds__(EsFftSeq<SEQ>::threads, 1) es_fft_degrid_rows_
         in.any = 0u;
         in.bf = 0u;
         LinearOut<T2, false, true, true> out;
-        out.sparse = (occupied * 8 < lay.ntile);
+        /* a butterfly of the last pass (stage 0, radix r) spreads its r
+         * outputs over the whole line: it is skipped with probability
+         * ~(1 - f)^r, f = occupied fraction; worth the r tests when f r is
+         * small (C4: 0.07, C5: 1.8, C2: 4) */
+        out.sparse = (occupied * ES_TILE * pl.stage[0].radix * 2 < gsz);
         out.bits = s_bits;
         out.base = planes + ((size_t) q * gsz + u) * gsz;
         out.estride = 1;
