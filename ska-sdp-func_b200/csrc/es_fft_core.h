@@ -696,17 +696,17 @@ ES_FFT_SEQ(1, 512, 28, 20, 11)     /* 6160: C2 */
 ES_FFT_SEQ(2, 640, 16, 14, 10, 11) /* 24640: C4, 96 registers */
 ES_FFT_SEQ(3, 512, 32, 24, 15)     /* 11520: C5 */
 ES_FFT_SEQ(4, 512, 15, 8, 8, 15)   /* 14400: C3 (fp64) */
-/* experiment: stage orders with fewer shared-memory bank conflicts */
-ES_FFT_SEQ(5, 640, 14, 11, 10, 16)
-ES_FFT_SEQ(6, 640, 10, 11, 14, 16)
-ES_FFT_SEQ(7, 512, 24, 15, 32)
-ES_FFT_SEQ(8, 512, 28, 11, 20)
-ES_FFT_SEQ(9, 512, 20, 11, 28)
-#define ES_FFT_NUM_SEQ 9
+/* Measured and not adopted (round 2, profiles/r02_logs/ab14_*): stage orders
+ * that halve the shared-memory bank conflicts of the middle passes
+ * (14.11.10.16, 24.15.32, 28.11.20: simulated wavefronts 1.17 / 1.08 / 1.00 x
+ * ideal against 1.38 / 1.50 / 1.14 x for the lists above) speed the row passes
+ * up by 3-9 % but put a large even radix last, where the gridding column pass
+ * pays more for the w-screen operands of 16-32 outputs per butterfly than it
+ * saves (C2 cols 9.8 -> 11.4 ms, C4 3.89 -> 4.05 s). */
+#define ES_FFT_NUM_SEQ 4
 /* (id, real type, is_double) of the kernel sets the Makefile builds (SEQ_IDS) */
 #define ES_FFT_SEQ_TABLE(X) X(1, float, 0) X(2, float, 0) X(3, float, 0) \
-    X(4, double, 1) X(5, float, 0) X(6, float, 0) X(7, float, 0) X(8, float, 0) \
-    X(9, float, 0)
+    X(4, double, 1)
 
 /* The line plan of a fixed stage list as compile-time constants: the same
  * arithmetic as es_fft_line_plan (es_fft_plan.c) -- lengths, strides, twiddle
