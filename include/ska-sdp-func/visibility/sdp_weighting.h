@@ -58,6 +58,35 @@ void sdp_weighting_uniform(
         sdp_Error* status
 );
 
+/*
+ * Briggs weighting that allocates nothing. NO COUNTERPART IN THE REFERENCE:
+ * added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it). Same arithmetic and output_weights as sdp_weighting_briggs,
+ * but the uv weight grid is not an argument: it is kept, with the two Briggs
+ * sums, in a file-scope device array of the library (8 MiB, held by every GPU
+ * that loads the library until exit).
+ *  - limit: grid_size * grid_size * num_pols <= 1,048,576 cells
+ *    (e.g. 1024^2 x 1 or 512^2 x 4); larger sizes return
+ *    SDP_ERR_INVALID_ARGUMENT;
+ *  - device (SDP_MEM_GPU) arrays only (SDP_ERR_MEM_LOCATION otherwise):
+ *    staging host arrays would allocate;
+ *  - calls no cudaMalloc / cudaFree and does not synchronise; work goes to
+ *    the legacy default stream;
+ *  - the array is shared by all calls and cleared at the start of each:
+ *    calls that overlap on the GPU (other streams or host threads) race.
+ */
+void sdp_weighting_briggs_no_alloc(
+        const sdp_Mem* uvw,
+        const sdp_Mem* freq_hz,
+        double max_abs_uv,
+        const double robust_param,
+        int64_t grid_size,
+        const sdp_Mem* input_weights,
+        sdp_Mem* output_weights,
+        sdp_Error* status
+);
+
 #ifdef __cplusplus
 }
 #endif

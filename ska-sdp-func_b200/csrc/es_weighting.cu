@@ -224,4 +224,94 @@ int es_weight_briggs(int64_t num_rows, int num_chan, int num_pols,
     return (int) cudaGetLastError();
 }
 
+/* ---- Briggs weighting without any allocation ----
+ * For callers that cannot call cudaMalloc (CUDA graph capture, serving
+ * loops): the uv weight grid and the two Briggs sums live in this file-scope
+ * device array instead of caller / cudaMalloc'ed memory. ES_WT_STATIC_CELLS
+ * (grid_size^2 x num_pols) doubles + 2: 8 MiB + 16 B on every GPU that loads
+ * the library, until exit. The array is shared by every call and keeps the
+ * last call's contents: each call clears what it uses; calls that overlap on
+ * the GPU (different streams or host threads) race on it.
+ * In host code `es_wt_scratch` is a host-side stand-in, not a device address:
+ * the address is asked for once per device (with that device current) by
+ * cudaGetSymbolAddress and that pointer is what the kernels get. */
+static __device__ __align__(256) double es_wt_scratch[ES_WT_STATIC_CELLS + 2];
+
+#define ES_WT_MAX_DEVICES 64
+static double* es_wt_scratch_ptr[ES_WT_MAX_DEVICES]; /* per device, 0 = not asked yet */
+
+int64_t es_weight_static_max_cells(void)
+{
+    return (int64_t) ES_WT_STATIC_CELLS;
+}
+
+/* As es_weight_briggs with grid and sums in the static scratch. Returns a
+ * cudaError_t as int; cudaErrorInvalidValue when the grid does not fit (the
+ * caller checks the size first and reports it). Calls no cudaMalloc /
+ * cudaFree: cudaGetSymbolAddress, cudaMemsetAsync and kernel launches only. */
+int es_weight_briggs_static(int64_t num_rows, int num_chan, int num_pols,
+        int64_t grid_size, const double* uvw, const double* freq_hz,
+        double max_abs_uv, double numerator, const void* input, void* output,
+        int is_double, void* stream)
+{
+    cudaStream_t s = (cudaStream_t) stream;
+    const int64_t cells = grid_size * grid_size * (int64_t) num_pols;
+    if (grid_size <= 0 || num_pols <= 0 || cells > (int64_t) ES_WT_STATIC_CELLS)
+        return (int) cudaErrorInvalidValue;
+    int dev = 0, sms = 0;
+    cudaError_t err = cudaGetDevice(&dev);
+    if (err != cudaSuccess) return (int) err;
+    if (dev < 0 || dev >= ES_WT_MAX_DEVICES) return (int) cudaErrorInvalidDevice;
+    if (!es_wt_scratch_ptr[dev])
+    {
+        /* set-up, once per device, that device being current */
+        double* ptr = 0;
+        err = cudaGetSymbolAddress((void**) &ptr, es_wt_scratch);
+        if (err != cudaSuccess) return (int) err;
+        es_wt_scratch_ptr[dev] = ptr;
+    }
+    double* scratch = es_wt_scratch_ptr[dev];
+    void* grid = (void*) scratch;                /* W[cells], W = float / double */
+    double* sums = scratch + ES_WT_STATIC_CELLS; /* [2] */
+    const int64_t total = num_rows * num_chan;
+    if (total == 0) return 0;
+    /* the array keeps the last call's contents: clear the cells this call
+     * accumulates into, and the sums */
+    err = cudaMemsetAsync(grid, 0, (size_t) cells * (is_double ? 8 : 4), s);
+    if (err == cudaSuccess) err = cudaMemsetAsync(sums, 0, 2 * sizeof(double), s);
+    if (err == cudaSuccess) err = cudaDeviceGetAttribute(&sms,
+            cudaDevAttrMultiProcessorCount, dev);
+    if (err != cudaSuccess) return (int) err;
+    const unsigned blocks = (unsigned) ((total + ES_WT_THREADS - 1) / ES_WT_THREADS);
+    unsigned rblocks = (unsigned) (sms * 8);
+    if (rblocks > blocks) rblocks = blocks;
+    if (is_double)
+    {
+        es_weight_grid_write_kernel<double><<<blocks, ES_WT_THREADS, 0, s>>>(
+                num_rows, num_chan, num_pols, grid_size, uvw, freq_hz,
+                max_abs_uv, (double*) grid, (const double*) input);
+        es_weight_sums_kernel<double><<<rblocks, ES_WT_THREADS, 0, s>>>(
+                num_rows, num_chan, num_pols, grid_size, uvw, freq_hz,
+                max_abs_uv, (const double*) grid, sums);
+        es_weight_read_kernel<double, true><<<blocks, ES_WT_THREADS, 0, s>>>(
+                num_rows, num_chan, num_pols, grid_size, uvw, freq_hz,
+                max_abs_uv, (const double*) grid, (const double*) input,
+                (double*) output, numerator, sums);
+    }
+    else
+    {
+        es_weight_grid_write_kernel<float><<<blocks, ES_WT_THREADS, 0, s>>>(
+                num_rows, num_chan, num_pols, grid_size, uvw, freq_hz,
+                max_abs_uv, (float*) grid, (const float*) input);
+        es_weight_sums_kernel<float><<<rblocks, ES_WT_THREADS, 0, s>>>(
+                num_rows, num_chan, num_pols, grid_size, uvw, freq_hz,
+                max_abs_uv, (const float*) grid, sums);
+        es_weight_read_kernel<float, true><<<blocks, ES_WT_THREADS, 0, s>>>(
+                num_rows, num_chan, num_pols, grid_size, uvw, freq_hz,
+                max_abs_uv, (const float*) grid, (const float*) input,
+                (float*) output, numerator, sums);
+    }
+    return (int) cudaGetLastError();
+}
+
 } // extern "C"

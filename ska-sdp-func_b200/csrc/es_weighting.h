@@ -26,6 +26,20 @@ int es_weight_briggs(int64_t num_rows, int num_chan, int num_pols,
         double max_abs_uv, double numerator, void* grid, const void* input,
         void* output, double* sums, int is_double, void* stream);
 
+/* Cells (grid_size^2 x num_pols) of the file-scope device array the
+ * allocation-free variant keeps its weight grid in (8 bytes each: 8 MiB). */
+#define ES_WT_STATIC_CELLS (1024 * 1024)
+int64_t es_weight_static_max_cells(void);
+
+/* es_weight_briggs with the grid and the sums in that static array (cleared
+ * per call; shared by all calls: overlapping calls race). No cudaMalloc /
+ * cudaFree; cudaErrorInvalidValue when grid_size^2 x num_pols exceeds
+ * ES_WT_STATIC_CELLS. */
+int es_weight_briggs_static(int64_t num_rows, int num_chan, int num_pols,
+        int64_t grid_size, const double* uvw, const double* freq_hz,
+        double max_abs_uv, double numerator, const void* input, void* output,
+        int is_double, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -310,3 +310,89 @@ void sdp_weighting_briggs(const sdp_Mem* uvw, const sdp_Mem* freq_hz,
     weighting(uvw, freq_hz, max_abs_uv, 1, robust_param, weight_grid_uv,
             input_weights, output_weights, status);
 }
+
+/* Briggs weighting for callers that cannot allocate (CUDA graph capture,
+ * serving loops): no counterpart in the reference; the weight grid is not an
+ * argument, it lives with the two sums in a file-scope device array of
+ * es_weighting.cu (ES_WT_STATIC_CELLS = 1 Mi cells, 8 MiB per GPU). Device
+ * (SDP_MEM_GPU) arrays only -- staging host arrays would allocate. Calls no
+ * cudaMalloc / cudaFree and does not synchronise; work is enqueued on the
+ * legacy default stream. */
+void sdp_weighting_briggs_no_alloc(const sdp_Mem* uvw, const sdp_Mem* freq_hz,
+        double max_abs_uv, const double robust_param, int64_t grid_size,
+        const sdp_Mem* input_weights, sdp_Mem* output_weights,
+        sdp_Error* status)
+{
+    if (*status) return;
+    sdp_MemType weights_type = SDP_MEM_VOID;
+    sdp_MemLocation location = sdp_mem_location(output_weights);
+    int64_t dims[4] = {0, 0, 0, 0};
+    weights_metadata(input_weights, &weights_type, &location, dims, status);
+    weights_metadata(output_weights, &weights_type, &location, dims, status);
+    if (*status) return;
+    if (location != SDP_MEM_GPU)
+    {
+        *status = SDP_ERR_MEM_LOCATION;
+        SDP_LOG_ERROR("sdp_weighting_briggs_no_alloc takes device (SDP_MEM_GPU) "
+                "arrays only: staging host arrays would need an allocation");
+        return;
+    }
+    check_uvw(uvw, location, dims[0], dims[1], status);
+    check_location(freq_hz, location, "freq_hz", status);
+    check_location(input_weights, location, "input_weights", status);
+    check_writeable(output_weights, "output_weights", status);
+    if (*status) return;
+    const int is_double = (weights_type == SDP_MEM_DOUBLE);
+    if (sdp_mem_type(uvw) != SDP_MEM_DOUBLE ||
+            sdp_mem_type(freq_hz) != SDP_MEM_DOUBLE ||
+            (weights_type != SDP_MEM_DOUBLE && weights_type != SDP_MEM_FLOAT) ||
+            sdp_mem_type(input_weights) != weights_type)
+    {
+        *status = SDP_ERR_DATA_TYPE;
+        SDP_LOG_ERROR("Unsupported data type(s)");
+        return;
+    }
+    if (sdp_mem_num_dims(freq_hz) != 1 ||
+            sdp_mem_shape_dim(freq_hz, 0) != dims[2] ||
+            dims[2] > INT32_MAX || dims[3] > INT32_MAX || dims[3] < 1 ||
+            !sdp_mem_is_c_contiguous(input_weights) ||
+            !sdp_mem_is_c_contiguous(output_weights))
+    {
+        *status = SDP_ERR_INVALID_ARGUMENT;
+        SDP_LOG_ERROR("freq_hz does not match the weights' [num_times, "
+                "num_baselines, num_channels, num_pols], or the weights are "
+                "not C contiguous");
+        return;
+    }
+    for (int i = 0; i < 4; ++i)
+        if (sdp_mem_shape_dim(input_weights, i) != dims[i])
+        {
+            *status = SDP_ERR_INVALID_ARGUMENT;
+            SDP_LOG_ERROR("input and output weights differ in shape");
+            return;
+        }
+    const int64_t max_cells = es_weight_static_max_cells();
+    if (grid_size < 1 || grid_size > max_cells ||
+            grid_size * grid_size > max_cells / dims[3])
+    {
+        *status = SDP_ERR_INVALID_ARGUMENT;
+        SDP_LOG_ERROR("sdp_weighting_briggs_no_alloc: grid_size^2 x num_pols = "
+                "%lld x %lld x %lld cells exceeds the static scratch of %lld "
+                "cells; use sdp_weighting_briggs with a caller-owned grid",
+                (long long) grid_size, (long long) grid_size,
+                (long long) dims[3], (long long) max_cells);
+        return;
+    }
+    const double numerator = pow(5.0 * 1 / (pow(10.0, robust_param)), 2.0);
+    const int rc = es_weight_briggs_static(dims[0] * dims[1], (int) dims[2],
+            (int) dims[3], grid_size, (const double*) sdp_mem_data_const(uvw),
+            (const double*) sdp_mem_data_const(freq_hz), max_abs_uv, numerator,
+            sdp_mem_data_const(input_weights), sdp_mem_data(output_weights),
+            is_double, 0);
+    if (rc != 0)
+    {
+        *status = SDP_ERR_RUNTIME;
+        SDP_LOG_ERROR("CUDA error: %s", cudaGetErrorString((cudaError_t) rc));
+        (void) cudaGetLastError();
+    }
+}

@@ -43,6 +43,21 @@ Lib.wrap_func(
     check_errcode=True,
 )
 
+Lib.wrap_func(
+    "sdp_weighting_briggs_no_alloc",
+    restype=None,
+    argtypes=[
+        Mem.handle_type(),
+        Mem.handle_type(),
+        ctypes.c_double,
+        ctypes.c_double,
+        ctypes.c_int64,
+        Mem.handle_type(),
+        Mem.handle_type(),
+    ],
+    check_errcode=True,
+)
+
 
 def get_uv_range(uvw, freq_hz):
     """Largest |u| in wavelengths at the last channel (the reference looks at
@@ -94,6 +109,24 @@ def uniform_weights(uvw, freq_hz, max_abs_uv, grid_uv, input_weights,
         Mem(freq_hz),
         max_abs_uv,
         Mem(grid_uv),
+        Mem(input_weights),
+        Mem(output_weights),
+    )
+
+
+def briggs_weights_no_alloc(uvw, freq_hz, max_abs_uv, robust_param, grid_size,
+                            input_weights, output_weights):
+    """:func:`briggs_weights` without any device allocation (no counterpart in
+    the reference): the uv weight grid is kept in a static device array of the
+    library instead of ``grid_uv``. Device arrays only;
+    ``grid_size**2 * num_pols`` must not exceed 1,048,576; calls that overlap
+    on the GPU race on the shared array."""
+    Lib.sdp_weighting_briggs_no_alloc(
+        Mem(uvw),
+        Mem(freq_hz),
+        max_abs_uv,
+        robust_param,
+        grid_size,
         Mem(input_weights),
         Mem(output_weights),
     )
