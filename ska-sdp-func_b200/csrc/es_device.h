@@ -72,7 +72,14 @@ int es_launch_tile_bounds(const EsGeom* g, const uint64_t* keys,
 int es_launch_build_records(const EsGeom* g, const void* uvw, const void* freq,
         const void* vis, const void* weight, const uint64_t* keys,
         const uint32_t* vals, int64_t num_entries, void* records,
-        const uint32_t* offsets, uint32_t* entry_pos, es_stream_t stream);
+        const uint32_t* offsets, uint32_t* entry_pos, void* kweights,
+        es_stream_t stream);
+
+/* Reals per record of the precomputed ES weights (kweights non-NULL above):
+ * ku[ns], kv[ns] (with the (-1)^(cell) signs folded in), kw[ns],
+ * ns = support + 1 -- plane-independent, so evaluated once per call instead
+ * of once per (record, plane) in the fp64 scatter. */
+size_t es_kweight_count(const EsGeom* g);
 
 /* ---- per batch of resident w-planes [first_plane, first_plane + nplanes) ---- */
 
@@ -121,8 +128,8 @@ size_t es_unit_bytes(void);                   /* bytes of one work unit */
 size_t es_partial_tile_bytes(int is_double);  /* bytes of one partial tile */
 
 /* Builds the work list of planes [first_plane, first_plane + nplanes):
- * per_plane != 0: one item per (tile, plane), else one per tile for the whole
- * range. Items with more than `split` records become several units (slices).
+ * per_plane != 0: one item per (tile, plane) (1: plane-major list, 2:
+ * tile-major list), else one per tile for the whole range. Items with more than `split` records become several units (slices).
  * counters: 8 x uint32 on the device ([0] = number of units afterwards);
  * split_done: max_split x uint32 completion counters. Both are zeroed here.
  * skip_empty != 0: items without records produce no unit. */
@@ -133,10 +140,12 @@ int es_launch_work_plan(const EsGeom* g, const uint64_t* keys,
         uint32_t* split_done, es_stream_t stream);
 
 /* Gridding: persistent CTAs execute the units; every cell of the nplanes
- * planes is written exactly once. scratch: max_partials partial tiles. */
+ * planes is written exactly once. scratch: max_partials partial tiles.
+ * kweights (fp64 only, may be NULL): ES weights per record from
+ * es_launch_build_records, es_kweight_count(g) reals per record. */
 int es_launch_scatter2(const EsGeom* g, const void* records, const void* units,
         uint32_t* counters, int first_plane, void* planes, void* scratch,
-        uint32_t* split_done, es_stream_t stream);
+        uint32_t* split_done, const void* kweights, es_stream_t stream);
 
 /* Degridding: persistent CTAs execute the units of a per_plane == 0 work
  * list (one record belongs to exactly one unit). */

@@ -70,6 +70,8 @@ struct sdp_GridderUvwEsFft
 
     /* presort work space (grow-only) */
     EsBuffer counts, offsets, keys_a, keys_b, vals_a, vals_b, records;
+    EsBuffer kweights;    /* fp64 gridding: ES weights per record (es_kweight_count) */
+    int have_kweights;    /* of the current call */
     EsBuffer tile_start, sort_temp, acc;
 
     /* load-balanced work units of the current plane batch */
@@ -326,7 +328,7 @@ void sdp_gridder_uvw_es_fft_free_plan(sdp_GridderUvwEsFft* plan)
         &plan->planes, &plan->fft_work, &plan->strip, &plan->image_t,
         &plan->counts, &plan->offsets,
         &plan->keys_a, &plan->keys_b, &plan->vals_a, &plan->vals_b,
-        &plan->records, &plan->tile_start, &plan->sort_temp, &plan->acc,
+        &plan->records, &plan->kweights, &plan->tile_start, &plan->sort_temp, &plan->acc,
         &plan->units, &plan->unit_counters, &plan->split_done, &plan->partials,
         &plan->occ, &plan->occ_totals,
         &plan->st_uvw, &plan->st_freq, &plan->st_vis, &plan->st_weight,
@@ -899,6 +901,15 @@ static void presort(sdp_GridderUvwEsFft* plan, const EsArrays* a,
     buffer_reserve(&plan->vals_a, (size_t) m * sizeof(uint32_t), status);
     buffer_reserve(&plan->vals_b, (size_t) m * sizeof(uint32_t), status);
     buffer_reserve(&plan->records, (size_t) m * rec_bytes, status);
+    /* fp64 gridding: the plane-independent ES weights of every record, once
+     * per call (the fp64 scatter spent most of its time re-evaluating them
+     * per plane); SKA_SDP_FUNC_ES_NO_KWEIGHTS=1: tests of the in-kernel path */
+    const int use_kweights = for_gridding && g->is_double &&
+            !getenv("SKA_SDP_FUNC_ES_NO_KWEIGHTS");
+    plan->have_kweights = use_kweights;
+    if (use_kweights)
+        buffer_reserve(&plan->kweights, (size_t) m * es_kweight_count(g) *
+                sizeof(double), status);
     if (*status) return;
 
     ES_CUDA(es_launch_emit_entries(g, a->uvw, a->freq,
@@ -927,7 +938,8 @@ static void presort(sdp_GridderUvwEsFft* plan, const EsArrays* a,
             (const uint64_t*) plan->keys_b.ptr,
             (const uint32_t*) plan->vals_b.ptr, m, plan->records.ptr,
             (const uint32_t*) plan->offsets.ptr,
-            for_gridding ? 0 : (uint32_t*) plan->vals_a.ptr, s));
+            for_gridding ? 0 : (uint32_t*) plan->vals_a.ptr,
+            use_kweights ? plan->kweights.ptr : 0, s));
     plan->stats.kernel_launches += 3;
     *num_entries = m;
 }
@@ -1124,6 +1136,12 @@ void sdp_grid_uvw_es_fft(sdp_GridderUvwEsFft* plan, const sdp_Mem* uvw,
     if (*status) return;
     event_mark(plan, 1);
 
+    /* order of the scatter's work list: plane-major, or tile-major where the
+     * per-record weight tables are re-read per plane (fp64);
+     * SKA_SDP_FUNC_ES_UNIT_ORDER=1|2 overrides (experiments) */
+    int unit_order = plan->have_kweights ? 2 : 1;
+    if (getenv("SKA_SDP_FUNC_ES_UNIT_ORDER"))
+        unit_order = atoi(getenv("SKA_SDP_FUNC_ES_UNIT_ORDER")) == 2 ? 2 : 1;
     const int batch = even_batch(plan, g->plane_end - g->plane_begin);
     for (int first = g->plane_begin; first < g->plane_end; first += batch)
     {
@@ -1138,13 +1156,15 @@ void sdp_grid_uvw_es_fft(sdp_GridderUvwEsFft* plan, const sdp_Mem* uvw,
                     (uint32_t*) plan->occ.ptr,
                     (unsigned long long*) plan->occ_totals.ptr, s));
         ES_CUDA(es_launch_work_plan(g, (const uint64_t*) plan->keys_b.ptr,
-                (const uint32_t*) plan->tile_start.ptr, first, nb, 1,
+                (const uint32_t*) plan->tile_start.ptr, first, nb,
+                unit_order,
                 lim.split, lim.max_units, ES_MAX_SPLIT_ITEMS, lim.max_partials,
                 plan->pruned_fft ? 1 : 0, plan->units.ptr, (uint32_t*) plan->unit_counters.ptr,
                 (uint32_t*) plan->split_done.ptr, s));
         ES_CUDA(es_launch_scatter2(g, plan->records.ptr, plan->units.ptr,
                 (uint32_t*) plan->unit_counters.ptr, first, plan->planes.ptr,
-                plan->partials.ptr, (uint32_t*) plan->split_done.ptr, s));
+                plan->partials.ptr, (uint32_t*) plan->split_done.ptr,
+                plan->have_kweights ? plan->kweights.ptr : 0, s));
         plan->stats.kernel_launches += 1;
         stage_mark(plan);
         if (plan->pruned_fft)

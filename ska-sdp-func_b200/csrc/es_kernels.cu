@@ -172,7 +172,8 @@ __global__ void __launch_bounds__(256) es_build_records_kernel(EsGeom g,
         const T* __restrict__ weight, const uint64_t* __restrict__ keys,
         const uint32_t* __restrict__ vals, int64_t num_entries,
         typename Prec<T>::Rec* __restrict__ records,
-        const uint32_t* __restrict__ offsets, uint32_t* __restrict__ entry_pos)
+        const uint32_t* __restrict__ offsets, uint32_t* __restrict__ entry_pos,
+        T* __restrict__ kweights)
 {
     const int64_t e = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= num_entries) return;
@@ -207,6 +208,26 @@ __global__ void __launch_bounds__(256) es_build_records_kernel(EsGeom g,
         r.vim = (T) 0;
     }
     records[e] = r;
+    if (kweights)
+    {
+        /* exactly the expressions of the scatter's staging loop
+         * (es_scatter.cu; kernels.cu:201-221, signs of :233-235) */
+        const int ns = g.support + 1;
+        const T beta = (T) g.beta;
+        const T inv_hs = (T) (2.0 / (double) g.support);
+        T* kr = kweights + (size_t) e * (size_t) (3 * ns);
+        const int lu0 = r.lu0, lv0 = r.lv0;
+        for (int k = 0; k < ns; ++k)
+        {
+            T ku = es_psi(beta, ((T) k + r.du) * inv_hs);
+            T kv = es_psi(beta, ((T) k + r.dv) * inv_hs);
+            if ((lu0 + k) & 1) ku = -ku;
+            if ((lv0 + k) & 1) kv = -kv;
+            kr[k] = ku;
+            kr[ns + k] = kv;
+            kr[2 * ns + k] = es_psi(beta, ((T) k + r.dw) * inv_hs);
+        }
+    }
 }
 
 template<typename T>
@@ -608,6 +629,11 @@ static int launch_gather2_ts(const EsGeom* g, const void* records,
 
 extern "C" {
 
+size_t es_kweight_count(const EsGeom* g)
+{
+    return (size_t) (3 * (g->support + 1));
+}
+
 size_t es_record_bytes(int is_double)
 {
     return is_double ? sizeof(EsRecD) : sizeof(EsRecF);
@@ -680,7 +706,8 @@ int es_launch_tile_bounds(const EsGeom* g, const uint64_t* keys,
 int es_launch_build_records(const EsGeom* g, const void* uvw, const void* freq,
         const void* vis, const void* weight, const uint64_t* keys,
         const uint32_t* vals, int64_t num_entries, void* records,
-        const uint32_t* offsets, uint32_t* entry_pos, es_stream_t stream)
+        const uint32_t* offsets, uint32_t* entry_pos, void* kweights,
+        es_stream_t stream)
 {
     if (num_entries == 0) return 0;
     cudaStream_t s = (cudaStream_t) stream;
@@ -688,12 +715,14 @@ int es_launch_build_records(const EsGeom* g, const void* uvw, const void* freq,
         es_build_records_kernel<double><<<blocks_for(num_entries, 256), 256, 0,
                 s>>>(*g, (const double*) uvw, (const double*) freq,
                 (const double2*) vis, (const double*) weight, keys, vals,
-                num_entries, (EsRecD*) records, offsets, entry_pos);
+                num_entries, (EsRecD*) records, offsets, entry_pos,
+                (double*) kweights);
     else
         es_build_records_kernel<float><<<blocks_for(num_entries, 256), 256, 0,
                 s>>>(*g, (const float*) uvw, (const float*) freq,
                 (const float2*) vis, (const float*) weight, keys, vals,
-                num_entries, (EsRecF*) records, offsets, entry_pos);
+                num_entries, (EsRecF*) records, offsets, entry_pos,
+                (float*) kweights);
     return (int) cudaGetLastError();
 }
 

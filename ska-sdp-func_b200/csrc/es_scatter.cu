@@ -63,6 +63,14 @@ __global__ void __launch_bounds__(256) es_work_plan_kernel(EsGeom g,
          * stores of concurrently running CTAs fall into the same plane rows */
         q = per_plane ? i / ntiles : 0;
         tile = per_plane ? i - q * ntiles : i;
+        if (per_plane == 2)
+        {
+            /* tile-major (fp64 gridding with per-record weight tables): the
+             * planes of one tile are consecutive units, so the records and
+             * weights of the tile are re-read from L2 instead of HBM */
+            tile = i / nplanes;
+            q = i - tile * nplanes;
+        }
         const int p_lo = first_plane + q;
         const int p_hi = per_plane ? p_lo : first_plane + nplanes - 1;
         es_entry_range(g, keys, tile_start, tile, p_lo, p_hi, a, b);
@@ -165,7 +173,7 @@ __global__ void __launch_bounds__(ES_SC_THREADS) es_scatter2_kernel(EsGeom g,
         const EsUnit* __restrict__ units, uint32_t* __restrict__ counters,
         int first_plane, typename Prec<T>::T2* __restrict__ planes,
         typename Prec<T>::T2* __restrict__ scratch,
-        uint32_t* __restrict__ split_done)
+        uint32_t* __restrict__ split_done, const T* __restrict__ kweights)
 {
     typedef typename Prec<T>::T2 T2;
     typedef typename Prec<T>::Rec Rec;
@@ -325,9 +333,140 @@ __global__ void __launch_bounds__(ES_SC_THREADS) es_scatter2_kernel(EsGeom g,
         }
         else
         {
-        /* fp64: the ES weights are too expensive to evaluate twice for
-         * records touching two bands: CTA-wide staging, one record per
-         * thread, then the band walk */
+        if (kweights)
+        {
+            /* fp64 with the ES weights of every record already evaluated
+             * (es_build_records_kernel: ku[ns], kv[ns] with the signs folded
+             * in, kw[ns] -- they do not depend on the plane): the
+             * warp-independent walk of the fp32 path, no CTA barrier inside a
+             * unit. 32 records per step, one per lane (header, w weight);
+             * those touching the warp's band are staged WCH at a time (lanes
+             * k < ns copy ku[k], kv[k] x visibility) and accumulated in
+             * record order. ncu on the CTA-wide form below (C3): 44 % of the
+             * stall samples at its chunk barrier, 20 % issue-active. */
+            constexpr int WCH = CHUNK / (ES_SC_THREADS / 32); /* per warp */
+            T* w_ku = s_ku + warp * WCH * NS;
+            T* w_kre = s_kre + warp * WCH * NS;
+            T* w_kim = s_kim + warp * WCH * NS;
+            int* w_pos = s_pos + warp * WCH;
+            const int kstride = 3 * ns;
+            for (uint32_t base = u.a; base < u.b; base += 32)
+            {
+                const uint32_t idx = base + (uint32_t) lane;
+                bool mine = false;
+                T vre = (T) 0, vim = (T) 0;
+                int lu0 = 0, lv0 = 0;
+                if (idx < u.b)
+                {
+                    const Rec& r = records[idx];
+                    lu0 = r.lu0;
+                    lv0 = r.lv0;
+                    mine = max(lu0, band_lo) <= min(lu0 + ns - 1, band_hi);
+                    if (mine)
+                    {
+                        const int dp = plane - r.p0;
+                        const T kw = (dp >= 0 && dp <= g.support) ?
+                                kweights[(size_t) idx * kstride + 2 * ns + dp] :
+                                (T) 0;
+                        vre = r.vre * kw;
+                        vim = r.vim * kw;
+                    }
+                }
+                unsigned m = __ballot_sync(0xffffffffu, mine);
+                while (m) /* warp-uniform */
+                {
+                    __syncwarp(); /* the previous batch's weights are consumed */
+                    /* all global loads of the batch first (the weights come
+                     * from L2 / HBM: their latencies overlap), then the
+                     * shared-memory stores */
+                    int cnt = 0;
+                    T bku[WCH], bkv[WCH], bvre[WCH], bvim[WCH];
+                    int bpos[WCH];
+#pragma unroll
+                    for (int j = 0; j < WCH; ++j)
+                    {
+                        bku[j] = bkv[j] = bvre[j] = bvim[j] = (T) 0;
+                        bpos[j] = 0;
+                        if (m)
+                        {
+                            const int src = __ffs((int) m) - 1;
+                            m &= m - 1u;
+                            ++cnt;
+                            bvre[j] = __shfl_sync(0xffffffffu, vre, src);
+                            bvim[j] = __shfl_sync(0xffffffffu, vim, src);
+                            const int slu = __shfl_sync(0xffffffffu, lu0, src);
+                            const int slv = __shfl_sync(0xffffffffu, lv0, src);
+                            bpos[j] = (slu << 16) | (slv & 0xffff);
+                            if (lane < ns)
+                            {
+                                const T* kr = kweights +
+                                        (size_t) (base + (uint32_t) src) * kstride;
+                                bku[j] = kr[lane];
+                                bkv[j] = kr[ns + lane];
+                            }
+                        }
+                    }
+#pragma unroll
+                    for (int j = 0; j < WCH; ++j)
+                    {
+                        if (j < cnt)
+                        {
+                            if (lane < ns)
+                            {
+                                w_ku[j * NS + lane] = bku[j];
+                                w_kre[j * NS + lane] = bvre[j] * bkv[j];
+                                w_kim[j * NS + lane] = bvim[j] * bkv[j];
+                            }
+                            if (lane == 0) w_pos[j] = bpos[j];
+                        }
+                    }
+                    __syncwarp();
+                    for (int e = 0; e < cnt; ++e)
+                    {
+                        const int pos = w_pos[e];
+                        const int elu0 = pos >> 16;
+                        const int r_lo = max(elu0, band_lo);
+                        const int r_hi = min(elu0 + ns - 1, band_hi);
+                        const int col = (int) (short) (pos & 0xffff) + c;
+                        if (lane_active && col >= 0 && col < cols_valid)
+                        {
+                            const T pre = w_kre[e * NS + c], pim = w_kim[e * NS + c];
+                            constexpr int MS = (NS <= 9) ? 3 : 4;
+                            for (int rb = r_lo + rsub; rb <= r_hi; rb += MS * rps)
+                            {
+                                T2 cell[MS];
+                                T ku[MS];
+#pragma unroll
+                                for (int mm = 0; mm < MS; ++mm)
+                                {
+                                    const int rr = rb + mm * rps;
+                                    if (rr <= r_hi)
+                                    {
+                                        ku[mm] = w_ku[e * NS + (rr - elu0)];
+                                        cell[mm] = tile[rr * ES_TILE + col];
+                                    }
+                                }
+#pragma unroll
+                                for (int mm = 0; mm < MS; ++mm)
+                                {
+                                    const int rr = rb + mm * rps;
+                                    if (rr <= r_hi)
+                                    {
+                                        cell[mm].x += pre * ku[mm];
+                                        cell[mm].y += pim * ku[mm];
+                                        tile[rr * ES_TILE + col] = cell[mm];
+                                    }
+                                }
+                            }
+                        }
+                    }
+                }
+            }
+        }
+        else
+        /* fp64 without precomputed weights: the ES weights are too expensive
+         * to evaluate twice for records touching two bands: CTA-wide staging,
+         * one record per thread, then the band walk */
         for (uint32_t chunk = u.a; chunk < u.b; chunk += CHUNK)
         {
             const int n = (int) min((uint32_t) CHUNK, u.b - chunk);
@@ -476,7 +615,7 @@ size_t scatter2_smem()
 template<typename T, int NS>
 int launch_scatter2_t(const EsGeom* g, const void* records, const void* units,
         uint32_t* counters, int first_plane, void* planes, void* scratch,
-        uint32_t* split_done, cudaStream_t s)
+        uint32_t* split_done, const void* kweights, cudaStream_t s)
 {
     typedef typename Prec<T>::T2 T2;
     typedef typename Prec<T>::Rec Rec;
@@ -506,7 +645,7 @@ int launch_scatter2_t(const EsGeom* g, const void* records, const void* units,
     }
     es_scatter2_kernel<T, NS><<<grid_size, ES_SC_THREADS, smem, s>>>(*g,
             (const Rec*) records, (const EsUnit*) units, counters, first_plane,
-            (T2*) planes, (T2*) scratch, split_done);
+            (T2*) planes, (T2*) scratch, split_done, (const T*) kweights);
     return (int) cudaGetLastError();
 }
 
@@ -564,7 +703,7 @@ int es_launch_work_plan(const EsGeom* g, const uint64_t* keys,
 
 int es_launch_scatter2(const EsGeom* g, const void* records, const void* units,
         uint32_t* counters, int first_plane, void* planes, void* scratch,
-        uint32_t* split_done, es_stream_t stream)
+        uint32_t* split_done, const void* kweights, es_stream_t stream)
 {
     cudaStream_t s = (cudaStream_t) stream;
     /* footprint slots per axis the kernel is unrolled for: 9, 13 or 17 */
@@ -572,18 +711,18 @@ int es_launch_scatter2(const EsGeom* g, const void* records, const void* units,
     if (g->is_double)
     {
         if (ns <= 9) return launch_scatter2_t<double, 9>(g, records, units,
-                counters, first_plane, planes, scratch, split_done, s);
+                counters, first_plane, planes, scratch, split_done, kweights, s);
         if (ns <= 13) return launch_scatter2_t<double, 13>(g, records, units,
-                counters, first_plane, planes, scratch, split_done, s);
+                counters, first_plane, planes, scratch, split_done, kweights, s);
         return launch_scatter2_t<double, 17>(g, records, units, counters,
-                first_plane, planes, scratch, split_done, s);
+                first_plane, planes, scratch, split_done, kweights, s);
     }
     if (ns <= 9) return launch_scatter2_t<float, 9>(g, records, units,
-            counters, first_plane, planes, scratch, split_done, s);
+            counters, first_plane, planes, scratch, split_done, kweights, s);
     if (ns <= 13) return launch_scatter2_t<float, 13>(g, records, units,
-            counters, first_plane, planes, scratch, split_done, s);
+            counters, first_plane, planes, scratch, split_done, kweights, s);
     return launch_scatter2_t<float, 17>(g, records, units, counters,
-            first_plane, planes, scratch, split_done, s);
+            first_plane, planes, scratch, split_done, kweights, s);
 }
 
 } // extern "C"

@@ -274,3 +274,20 @@ def test_twiddles_in_global_memory_mode(monkeypatch, single):
     monkeypatch.setenv("SKA_SDP_FUNC_ES_FFT_TW_GLOBAL", "1")
     c = synth.reference_test_case(256, num_vis=300, num_chan=6, single=single)
     check_parity(c, 1e-5 if single else 1e-9, True)
+
+
+@pytest.mark.parametrize("precomputed", [True, False])
+def test_fp64_scatter_weight_paths_agree_bitwise(monkeypatch, precomputed):
+    """fp64 gridding evaluates the plane-independent ES weights of every
+    record once per call (es_build_records_kernel -> kweights) instead of once
+    per (record, plane) inside the scatter; SKA_SDP_FUNC_ES_NO_KWEIGHTS=1 keeps
+    the in-kernel evaluation. Same expressions in the same order: the two
+    dirty images are bitwise equal, and both match the oracle."""
+    c = synth.mid_like_predict(40, 1, 16, 512, seed=42, single=False)
+    if not precomputed:
+        monkeypatch.setenv("SKA_SDP_FUNC_ES_NO_KWEIGHTS", "1")
+    dirty, _ = product_grid(c, 1e-10, True)
+    assert rel_max(dirty, oracle_grid(c, 1e-10, True)) <= TOL[np.dtype(np.float64)]
+    monkeypatch.delenv("SKA_SDP_FUNC_ES_NO_KWEIGHTS", raising=False)
+    dirty2, _ = product_grid(c, 1e-10, True)
+    assert np.array_equal(dirty, dirty2)
