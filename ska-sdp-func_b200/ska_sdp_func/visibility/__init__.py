@@ -1,7 +1,9 @@
 """Visibility-domain functions (same module layout as the reference's
-``ska_sdp_func.visibility``): uv-grid weighting."""
+``ska_sdp_func.visibility``): uv-grid weighting and the tiled presort."""
+from .tiled_functions import bucket_sort, count_and_prefix_sum, tiled_indexing
 from .weighting import (briggs_weights, briggs_weights_no_alloc, get_uv_range,
                         uniform_weights)
 
-__all__ = ["briggs_weights", "briggs_weights_no_alloc", "get_uv_range",
+__all__ = ["briggs_weights", "briggs_weights_no_alloc", "bucket_sort",
+           "count_and_prefix_sum", "get_uv_range", "tiled_indexing",
            "uniform_weights"]
