@@ -34,6 +34,7 @@
  */
 #include <stdint.h>
 #include <stdlib.h>
+#include <string.h>
 
 #include <cooperative_groups.h>
 #include <cuda_runtime.h>
@@ -99,9 +100,21 @@ __device__ __forceinline__ float subtract(const float r, const float gain,
             __dmul_rn(__dmul_rn((double) gain, peak), (double) psf));
 }
 
-/* All minor cycles. `slice` = elements per CTA; IN_SMEM: the CTA's slice
- * lives in dynamic shared memory between the first load and the final store. */
-template<typename T, bool IN_SMEM>
+/* All minor cycles. `slice` = elements per CTA. MODE:
+ *  ES_CLEAN_GLOBAL  slices stay in global memory / L2 (images too large for
+ *                   the shared memory of the grid), exchange through global
+ *                   candidates + grid barrier;
+ *  ES_CLEAN_SMEM    the CTA's slice lives in dynamic shared memory between the
+ *                   first load and the final store, same exchange;
+ *  ES_CLEAN_CLUSTER the grid is ONE thread-block cluster (8 or 16 CTAs; small
+ *                   images): slices in shared memory, candidates in each
+ *                   CTA's shared memory, read by the others through
+ *                   distributed shared memory after the hardware cluster
+ *                   barrier -- no global-memory round trip in the exchange. */
+#define ES_CLEAN_GLOBAL 0
+#define ES_CLEAN_SMEM 1
+#define ES_CLEAN_CLUSTER 2
+template<typename T, int MODE>
 __global__ void __launch_bounds__(ES_CLEAN_THREADS) es_hogbom_cycles_kernel(
         const int64_t n, const int64_t slice, const T* __restrict__ psf,
         const T gain, const T threshold, const int cycle_limit,
@@ -109,13 +122,14 @@ __global__ void __launch_bounds__(ES_CLEAN_THREADS) es_hogbom_cycles_kernel(
         Cand* __restrict__ cand, Header* __restrict__ header,
         int* __restrict__ components)
 {
+    constexpr bool IN_SMEM = MODE != ES_CLEAN_GLOBAL;
     extern __shared__ __align__(16) unsigned char s_raw[];
+    __shared__ Cand s_cand[2];
     __shared__ double s_val[ES_CLEAN_THREADS / 32];
     __shared__ long long s_idx[ES_CLEAN_THREADS / 32];
     __shared__ double s_peak;
     __shared__ long long s_peak_idx;
 
-    cg::grid_group grid = cg::this_grid();
     const int64_t total = n * n;
     const int64_t lo = (int64_t) blockIdx.x * slice;
     const int64_t hi = lo + slice < total ? lo + slice : total;
@@ -156,37 +170,59 @@ __global__ void __launch_bounds__(ES_CLEAN_THREADS) es_hogbom_cycles_kernel(
                 Cand c;
                 c.val = v;
                 c.idx = i;
-                cand[(size_t) (cycle & 1) * gridDim.x + blockIdx.x] = c;
+                if (MODE == ES_CLEAN_CLUSTER)
+                    s_cand[cycle & 1] = c;
+                else
+                    cand[(size_t) (cycle & 1) * gridDim.x + blockIdx.x] = c;
             }
         }
-        grid.sync();
+        /* all candidates of this cycle published: the one meeting point of a
+         * cycle (cooperative_groups' grid barrier; a hand-rolled counter
+         * barrier measured the same, profiles/r02_logs/clean_barrier_job31.txt) */
+        if (MODE == ES_CLEAN_CLUSTER)
+            cg::this_cluster().sync();
+        else
+            cg::this_grid().sync();
         /* every CTA reduces all candidates to the same peak */
         if (warp == 0)
         {
             double v = 0.0;
             long long i = -1;
-            const Cand* all = cand + (size_t) (cycle & 1) * gridDim.x;
-            for (unsigned c0 = lane; c0 < gridDim.x; c0 += 32 * 8)
+            if (MODE == ES_CLEAN_CLUSTER)
             {
-                /* written by other SMs in this cycle: read past L1, eight
-                 * loads in flight */
-                double ov[8];
-                long long oi[8];
-#pragma unroll
-                for (int u = 0; u < 8; ++u)
+                if (lane < (int) gridDim.x)
                 {
-                    const unsigned c = c0 + 32 * u;
-                    oi[u] = -1;
-                    ov[u] = 0.0;
-                    if (c < gridDim.x)
-                    {
-                        ov[u] = __ldcg(&all[c].val);
-                        oi[u] = __ldcg(&all[c].idx);
-                    }
+                    const Cand* theirs = cg::this_cluster().map_shared_rank(
+                            &s_cand[cycle & 1], lane);
+                    v = theirs->val;
+                    i = theirs->idx;
                 }
+            }
+            else
+            {
+                const Cand* all = cand + (size_t) (cycle & 1) * gridDim.x;
+                for (unsigned c0 = lane; c0 < gridDim.x; c0 += 32 * 8)
+                {
+                    /* written by other SMs in this cycle: read past L1, eight
+                     * loads in flight */
+                    double ov[8];
+                    long long oi[8];
 #pragma unroll
-                for (int u = 0; u < 8; ++u)
-                    if (beats(ov[u], oi[u], v, i)) { v = ov[u]; i = oi[u]; }
+                    for (int u = 0; u < 8; ++u)
+                    {
+                        const unsigned c = c0 + 32 * u;
+                        oi[u] = -1;
+                        ov[u] = 0.0;
+                        if (c < gridDim.x)
+                        {
+                            ov[u] = __ldcg(&all[c].val);
+                            oi[u] = __ldcg(&all[c].idx);
+                        }
+                    }
+#pragma unroll
+                    for (int u = 0; u < 8; ++u)
+                        if (beats(ov[u], oi[u], v, i)) { v = ov[u]; i = oi[u]; }
+                }
             }
             warp_best(v, i);
             if (lane == 0) { s_peak = v; s_peak_idx = i; }
@@ -196,13 +232,12 @@ __global__ void __launch_bounds__(ES_CLEAN_THREADS) es_hogbom_cycles_kernel(
         const long long peak_idx = s_peak_idx;
         /* stop: cycle limit, or peak below the threshold (.cpp:199-202) */
         if (cycle >= cycle_limit || peak_idx < 0 || (T) peak < threshold) break;
-        if (blockIdx.x == 0 && threadIdx.x == 0)
-        {
-            /* clean_comp[peak] += loop_gain * highest_value (.cpp:211-214) */
-            const T before = clean_model[peak_idx];
-            if (before == (T) 0) components[num_components++] = (int) peak_idx;
-            clean_model[peak_idx] = before + (T) __dmul_rn((double) gain, peak);
-        }
+        /* clean_comp[peak] += loop_gain * highest_value (.cpp:211-214), by
+         * one thread of the grid: its load is issued here and used after the
+         * subtraction pass, off the critical path of the cycle */
+        const bool writer = blockIdx.x == 0 && threadIdx.x == 0;
+        T before = (T) 0;
+        if (writer) before = __ldcg(clean_model + peak_idx);
         /* subtract the shifted PSF from the slice, look for the next peak */
         const int64_t mx = peak_idx / n, my = peak_idx - mx * n;
         const T* window = psf + (n - mx) * 2 * n + (n - my);
@@ -240,11 +275,19 @@ __global__ void __launch_bounds__(ES_CLEAN_THREADS) es_hogbom_cycles_kernel(
                 }
             }
         }
+        if (writer)
+        {
+            if (before == (T) 0) components[num_components++] = (int) peak_idx;
+            __stcg(clean_model + peak_idx,
+                    before + (T) __dmul_rn((double) gain, peak));
+        }
         __syncthreads();
     }
     if (IN_SMEM)
         for (int64_t k = threadIdx.x; k < mine; k += ES_CLEAN_THREADS)
             residual[lo + k] = res[k];
+    /* nobody may still be reading this CTA's candidates when it exits */
+    if (MODE == ES_CLEAN_CLUSTER) cg::this_cluster().sync();
     if (blockIdx.x == 0 && threadIdx.x == 0)
     {
         header->cycles_done = cycle;
@@ -337,51 +380,106 @@ int run(const int64_t n, const T* psf, const double loop_gain,
             cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
     if (!coop || sms < 1) return (int) cudaErrorNotSupported;
 
-    /* few elements per thread and cycle; at most one CTA per SM */
     const int64_t total = n * n;
-    int per_thread = 4;
-    if (const char* e = getenv("SKA_SDP_FUNC_CLEAN_PER_THREAD"))
-        if (atoi(e) > 0) per_thread = atoi(e);
-    int64_t ctas = (total + per_thread * ES_CLEAN_THREADS - 1) /
-            (per_thread * ES_CLEAN_THREADS);
-    int64_t cap = sms;
-    if (const char* e = getenv("SKA_SDP_FUNC_CLEAN_MAX_CTAS"))
-        if (atoi(e) > 0 && atoi(e) < sms) cap = atoi(e);
-    if (ctas > cap) ctas = cap;
-    if (ctas > ES_CLEAN_MAX_CTAS) ctas = ES_CLEAN_MAX_CTAS;
-    if (ctas < 1) ctas = 1;
-    /* slices of whole rows (aligned, coalesced PSF windows) where there are
-     * enough rows, else of whole CTA strides */
-    int64_t slice = (total + ctas - 1) / ctas;
-    const int64_t unit = n >= 2 * ctas ? n : ES_CLEAN_THREADS;
-    slice = (slice + unit - 1) / unit * unit;
-    ctas = (total + slice - 1) / slice;
-    const size_t slice_bytes = (size_t) slice * sizeof(T);
-    const bool in_smem = slice_bytes + 1024 <= (size_t) smem_max;
-
     const T gain = (T) loop_gain, thr = (T) threshold;
+    int64_t slice = 0;
     void* args[] = {(void*) &n, (void*) &slice, (void*) &psf, (void*) &gain,
             (void*) &thr, (void*) &cycle_limit, (void*) &residual,
             (void*) &clean_model, (void*) &cand, (void*) &header,
             (void*) &components};
-    const void* fn = in_smem ?
-            (const void*) es_hogbom_cycles_kernel<T, true> :
-            (const void*) es_hogbom_cycles_kernel<T, false>;
-    if (in_smem)
+    bool launched = false;
+
+    /* small images: ONE cluster of 16 (or 8) CTAs holds the whole residual in
+     * its shared memory and exchanges the candidates through it */
+    const char* no_cluster = getenv("SKA_SDP_FUNC_CLEAN_NO_CLUSTER");
+    for (int csize = 16; csize >= 8 && !launched &&
+            !(no_cluster && atoi(no_cluster) > 0); csize /= 2)
     {
-        err = cudaFuncSetAttribute(fn,
-                cudaFuncAttributeMaxDynamicSharedMemorySize, (int) slice_bytes);
+        int64_t rows = (n + csize - 1) / csize;
+        slice = rows * n;
+        const size_t slice_bytes = (size_t) slice * sizeof(T);
+        /* worth it while a thread has at most one group of PSF loads per
+         * cycle (measured: 256^2 4.2 vs 5.0 us per cycle, 512^2 8.7 vs 5.0) */
+        if (slice_bytes + 2048 > (size_t) smem_max ||
+                total < (int64_t) csize * ES_CLEAN_THREADS ||
+                slice > (int64_t) ES_CLEAN_UNROLL * ES_CLEAN_THREADS) continue;
+        const void* fn = (const void*) es_hogbom_cycles_kernel<T, ES_CLEAN_CLUSTER>;
+        if (cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                (int) slice_bytes) != cudaSuccess ||
+                (csize > 8 && cudaFuncSetAttribute(fn,
+                cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess))
+        {
+            (void) cudaGetLastError();
+            continue;
+        }
+        cudaLaunchConfig_t cfg;
+        memset(&cfg, 0, sizeof(cfg));
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = (unsigned) csize;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        cfg.gridDim = dim3((unsigned) ((total + slice - 1) / slice));
+        cfg.blockDim = dim3(ES_CLEAN_THREADS);
+        cfg.dynamicSmemBytes = slice_bytes;
+        cfg.stream = st;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        /* the cluster must be complete: rows that do not fill it fall back */
+        if (cfg.gridDim.x != (unsigned) csize) continue;
+        int clusters = 0;
+        if (cudaOccupancyMaxActiveClusters(&clusters, fn, &cfg) != cudaSuccess ||
+                clusters < 1)
+        {
+            (void) cudaGetLastError();
+            continue;
+        }
+        err = cudaLaunchKernelExC(&cfg, fn, args);
+        if (err != cudaSuccess) return (int) err;
+        launched = true;
+    }
+    if (!launched)
+    {
+        /* few elements per thread and cycle; at most one CTA per SM */
+        int per_thread = 4;
+        if (const char* e = getenv("SKA_SDP_FUNC_CLEAN_PER_THREAD"))
+            if (atoi(e) > 0) per_thread = atoi(e);
+        int64_t ctas = (total + per_thread * ES_CLEAN_THREADS - 1) /
+                (per_thread * ES_CLEAN_THREADS);
+        int64_t cap = sms;
+        if (const char* e = getenv("SKA_SDP_FUNC_CLEAN_MAX_CTAS"))
+            if (atoi(e) > 0 && atoi(e) < sms) cap = atoi(e);
+        if (ctas > cap) ctas = cap;
+        if (ctas > ES_CLEAN_MAX_CTAS) ctas = ES_CLEAN_MAX_CTAS;
+        if (ctas < 1) ctas = 1;
+        /* slices of whole rows (aligned, coalesced PSF windows) where there
+         * are enough rows, else of whole CTA strides */
+        slice = (total + ctas - 1) / ctas;
+        const int64_t unit = n >= 2 * ctas ? n : ES_CLEAN_THREADS;
+        slice = (slice + unit - 1) / unit * unit;
+        ctas = (total + slice - 1) / slice;
+        const size_t slice_bytes = (size_t) slice * sizeof(T);
+        const bool in_smem = slice_bytes + 2048 <= (size_t) smem_max;
+        const void* fn = in_smem ?
+                (const void*) es_hogbom_cycles_kernel<T, ES_CLEAN_SMEM> :
+                (const void*) es_hogbom_cycles_kernel<T, ES_CLEAN_GLOBAL>;
+        if (in_smem)
+        {
+            err = cudaFuncSetAttribute(fn,
+                    cudaFuncAttributeMaxDynamicSharedMemorySize,
+                    (int) slice_bytes);
+            if (err != cudaSuccess) return (int) err;
+        }
+        int per_sm = 0;
+        err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn,
+                ES_CLEAN_THREADS, in_smem ? slice_bytes : 0);
+        if (err != cudaSuccess) return (int) err;
+        if (per_sm < 1 || (int64_t) per_sm * sms < ctas)
+            return (int) cudaErrorCooperativeLaunchTooLarge;
+        err = cudaLaunchCooperativeKernel(fn, dim3((unsigned) ctas),
+                dim3(ES_CLEAN_THREADS), args, in_smem ? slice_bytes : 0, st);
         if (err != cudaSuccess) return (int) err;
     }
-    int per_sm = 0;
-    err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn,
-            ES_CLEAN_THREADS, in_smem ? slice_bytes : 0);
-    if (err != cudaSuccess) return (int) err;
-    if (per_sm < 1 || (int64_t) per_sm * sms < ctas)
-        return (int) cudaErrorCooperativeLaunchTooLarge;
-    err = cudaLaunchCooperativeKernel(fn, dim3((unsigned) ctas),
-            dim3(ES_CLEAN_THREADS), args, in_smem ? slice_bytes : 0, st);
-    if (err != cudaSuccess) return (int) err;
 
     if (dim > 0)
     {
