@@ -24,6 +24,9 @@ static void fail(sdp_Error code, const char* what, sdp_Error* status)
     SDP_LOG_ERROR("%s", what);
 }
 
+/* report and leave the (void) entry point */
+#define FAIL(code, what) do { fail(code, what, status); return; } while (0)
+
 static void cuda_failed(cudaError_t err, sdp_Error code, sdp_Error* status)
 {
     *status = code;
@@ -46,42 +49,40 @@ void sdp_hogbom_clean(const sdp_Mem* dirty_img, const sdp_Mem* psf,
 
     /* .cpp:760-853, in the reference's order */
     if (sdp_mem_is_read_only(skymodel))
-        return fail(SDP_ERR_RUNTIME, "Output is not writable", status);
+        FAIL(SDP_ERR_RUNTIME, "Output is not writable");
     if (sdp_mem_location(dirty_img) != sdp_mem_location(skymodel))
-        return fail(SDP_ERR_MEM_LOCATION, "Memory location mismatch", status);
+        FAIL(SDP_ERR_MEM_LOCATION, "Memory location mismatch");
     if (type != sdp_mem_type(psf))
-        return fail(SDP_ERR_DATA_TYPE, "The Dirty image and PSF must be of "
-                "the same data type", status);
+        FAIL(SDP_ERR_DATA_TYPE, "The Dirty image and PSF must be of "
+                "the same data type");
     if (type != sdp_mem_type(skymodel))
-        return fail(SDP_ERR_DATA_TYPE, "The input and output must be of the "
-                "same data type", status);
+        FAIL(SDP_ERR_DATA_TYPE, "The input and output must be of the "
+                "same data type");
     if (sdp_mem_shape_dim(clean_model, 0) != n)
-        return fail(SDP_ERR_RUNTIME, "The CLEAN model and the dirty image "
-                "must be the same size", status);
+        FAIL(SDP_ERR_RUNTIME, "The CLEAN model and the dirty image "
+                "must be the same size");
     if (sdp_mem_shape_dim(residual, 0) != n)
-        return fail(SDP_ERR_RUNTIME, "The residual image and the dirty image "
-                "must be the same size", status);
+        FAIL(SDP_ERR_RUNTIME, "The residual image and the dirty image "
+                "must be the same size");
     if (sdp_mem_shape_dim(skymodel, 0) != n)
-        return fail(SDP_ERR_RUNTIME, "The skymodel image and the dirty image "
-                "must be the same size", status);
+        FAIL(SDP_ERR_RUNTIME, "The skymodel image and the dirty image "
+                "must be the same size");
     if (sdp_mem_shape_dim(cbeam_details, 0) != 4)
-        return fail(SDP_ERR_RUNTIME, "The array describing the CLEAN beam "
-                "must include BMAJ, BMIN, THETA and SIZE", status);
+        FAIL(SDP_ERR_RUNTIME, "The array describing the CLEAN beam "
+                "must include BMAJ, BMIN, THETA and SIZE");
     if (n != n1)
-        return fail(SDP_ERR_RUNTIME, "Dirty image array must be square shaped",
-                status);
+        FAIL(SDP_ERR_RUNTIME, "Dirty image array must be square shaped");
     if (psf_dim != psf_dim1)
-        return fail(SDP_ERR_RUNTIME, "PSF array must be square shaped", status);
+        FAIL(SDP_ERR_RUNTIME, "PSF array must be square shaped");
     if (psf_dim != n * 2)
-        return fail(SDP_ERR_RUNTIME, "PSF array dimensions must be double the "
-                "Dirty image array dimensions", status);
+        FAIL(SDP_ERR_RUNTIME, "PSF array dimensions must be double the "
+                "Dirty image array dimensions");
     if (cycle_limit < 1)
-        return fail(SDP_ERR_RUNTIME, "Number of cycles to perform must be > 0",
-                status);
+        FAIL(SDP_ERR_RUNTIME, "Number of cycles to perform must be > 0");
     if (loop_gain <= 0)
-        return fail(SDP_ERR_RUNTIME, "Loop gain must be > 0", status);
+        FAIL(SDP_ERR_RUNTIME, "Loop gain must be > 0");
     if (type != SDP_MEM_DOUBLE && type != SDP_MEM_FLOAT)
-        return fail(SDP_ERR_DATA_TYPE, "Unsupported data type", status);
+        FAIL(SDP_ERR_DATA_TYPE, "Unsupported data type");
     /* what the kernels index without further checks */
     const sdp_Mem* images[] = {dirty_img, psf, clean_model, residual, skymodel};
     for (int k = 0; k < 5; ++k)
@@ -92,17 +93,16 @@ void sdp_hogbom_clean(const sdp_Mem* dirty_img, const sdp_Mem* psf,
                 sdp_mem_shape_dim(images[k], 1) != want ||
                 !sdp_mem_is_c_contiguous(images[k]) ||
                 sdp_mem_type(images[k]) != type)
-            return fail(SDP_ERR_RUNTIME, "The images must be square, C "
-                    "contiguous 2-D arrays of one data type", status);
+            FAIL(SDP_ERR_RUNTIME, "The images must be square, C "
+                    "contiguous 2-D arrays of one data type");
         if (sdp_mem_location(images[k]) != location)
-            return fail(SDP_ERR_MEM_LOCATION, "Memory location mismatch",
-                    status);
+            FAIL(SDP_ERR_MEM_LOCATION, "Memory location mismatch");
     }
     if (sdp_mem_is_read_only(clean_model) || sdp_mem_is_read_only(residual))
-        return fail(SDP_ERR_RUNTIME, "Output is not writable", status);
+        FAIL(SDP_ERR_RUNTIME, "Output is not writable");
     if (n < 1 || n > 46340 || sdp_mem_type(cbeam_details) != type)
-        return fail(SDP_ERR_RUNTIME, "Image size out of range, or the CLEAN "
-                "beam description is not of the images' data type", status);
+        FAIL(SDP_ERR_RUNTIME, "Image size out of range, or the CLEAN "
+                "beam description is not of the images' data type");
 
     /* CLEAN beam: [sigma_x, sigma_y, theta (degrees), size], .cpp:46-63 */
     double details[4] = {0.0, 0.0, 0.0, 0.0};
@@ -114,7 +114,10 @@ void sdp_hogbom_clean(const sdp_Mem* dirty_img, const sdp_Mem* psf,
             cudaError_t err = cudaMemcpy(&raw, sdp_mem_data_const(cbeam_details),
                     bytes, cudaMemcpyDeviceToHost);
             if (err != cudaSuccess)
-                return cuda_failed(err, SDP_ERR_MEM_COPY_FAILURE, status);
+            {
+                cuda_failed(err, SDP_ERR_MEM_COPY_FAILURE, status);
+                return;
+            }
         }
         else
         {
@@ -126,8 +129,8 @@ void sdp_hogbom_clean(const sdp_Mem* dirty_img, const sdp_Mem* psf,
     const int64_t cbeam_dim = (int64_t) details[3];
     if (cbeam_dim < 1 || cbeam_dim > 32768 || details[0] == 0.0 ||
             details[1] == 0.0)
-        return fail(SDP_ERR_RUNTIME, "The CLEAN beam needs non-zero widths "
-                "and a size of at least 1", status);
+        FAIL(SDP_ERR_RUNTIME, "The CLEAN beam needs non-zero widths "
+                "and a size of at least 1");
     const double theta = (M_PI / 180) * details[2];
     const double sx2 = details[0] * details[0], sy2 = details[1] * details[1];
     const double beam_a = pow(cos(theta), 2) / (2 * sx2) +
@@ -148,7 +151,10 @@ void sdp_hogbom_clean(const sdp_Mem* dirty_img, const sdp_Mem* psf,
     cudaError_t err = cudaMalloc((void**) &block, scratch_bytes +
             (on_host ? 7 * image_bytes + 1024 : 0));
     if (err != cudaSuccess)
-        return cuda_failed(err, SDP_ERR_MEM_ALLOC_FAILURE, status);
+    {
+        cuda_failed(err, SDP_ERR_MEM_ALLOC_FAILURE, status);
+        return;
+    }
     char* d_psf = (char*) sdp_mem_data_const(psf);
     char* d_model = (char*) sdp_mem_data(clean_model);
     char* d_residual = (char*) sdp_mem_data(residual);
