@@ -17,7 +17,8 @@
  *    thread owns CH consecutive channels of one row and, per source, evaluates
  *    two phasors (first channel, channel step) and ROTATES through the other
  *    channels (one fp64 complex product each, error ~ 1e-16 per step) instead
- *    of CH sincos evaluations;
+ *    of CH sincos evaluations; long runs rotate on up to four interleaved
+ *    chains (step r^4) so that no dependency chain is longer than 8 products;
  *  - lanes of a warp are consecutive rows of ONE channel group, so the source
  *    directions and the fluxes of the group are warp-uniform: they are staged
  *    in shared memory per chunk of sources (fluxes already cast to the
@@ -130,19 +131,37 @@ __global__ void __launch_bounds__(ES_DFT_THREADS) es_dft_kernel(
         for (int s = 0; s < ns; ++s)
         {
             const double l = s_dir[s][0], m = s_dir[s][1], n = s_dir[s][2];
-            double pc, ps, rc = 1.0, rs = 0.0;
+            /* NC interleaved rotation chains: channel j is on chain j % NC,
+             * which starts at p0 r^(j % NC) and advances by r^NC -- NC times
+             * shorter dependency chains for 5 more complex products */
+            constexpr int NC = !LINEAR ? 1 : CH >= 16 ? 4 : CH >= 8 ? 2 : 1;
+            double pc[NC], ps[NC], rc = 1.0, rs = 0.0;
             if (LINEAR)
             {
                 const double d = l * u[0] + m * v[0] + n * w[0];
-                phasor_of_turns(k0 * d, pc, ps);
+                phasor_of_turns(k0 * d, pc[0], ps[0]);
                 if (CH > 1) phasor_of_turns(dk * d, rc, rs);
+#pragma unroll
+                for (int c = 1; c < NC; ++c)
+                {
+                    pc[c] = pc[c - 1] * rc - ps[c - 1] * rs;
+                    ps[c] = pc[c - 1] * rs + ps[c - 1] * rc;
+                }
+#pragma unroll
+                for (int k = 1; k < NC; k *= 2)
+                {
+                    const double sq = rc * rc - rs * rs;
+                    rs = 2.0 * rc * rs;
+                    rc = sq;
+                }
             }
 #pragma unroll
             for (int j = 0; j < CH; ++j)
             {
+                const int c = j % NC;
                 if (!LINEAR)
-                    phasor_of_turns(l * u[j] + m * v[j] + n * w[j], pc, ps);
-                const A ac = (A) pc, as = (A) ps;
+                    phasor_of_turns(l * u[j] + m * v[j] + n * w[j], pc[0], ps[0]);
+                const A ac = (A) pc[c], as = (A) ps[c];
 #pragma unroll
                 for (int p = 0; p < P; ++p)
                 {
@@ -150,11 +169,11 @@ __global__ void __launch_bounds__(ES_DFT_THREADS) es_dft_kernel(
                     acc[j][p].x += ac * f.x - as * f.y;
                     acc[j][p].y += ac * f.y + as * f.x;
                 }
-                if (LINEAR && j + 1 < CH)
+                if (LINEAR && j + NC < CH)
                 {
-                    const double nc = pc * rc - ps * rs;
-                    ps = pc * rs + ps * rc;
-                    pc = nc;
+                    const double nc = pc[c] * rc - ps[c] * rs;
+                    ps[c] = pc[c] * rs + ps[c] * rc;
+                    pc[c] = nc;
                 }
             }
         }
