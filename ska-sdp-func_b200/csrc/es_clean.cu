@@ -63,15 +63,34 @@ __device__ __forceinline__ bool beats(const double av, const long long ai,
     return ai >= 0 && (bi < 0 || av > bv || (av == bv && ai < bi));
 }
 
+/* Warp arg-max with the tie rule of beats(), all lanes get the result. The
+ * value goes through an order-preserving 64-bit key (sign-magnitude -> biased)
+ * so that the hardware warp reductions (redux.sync, 32 bits) can be used:
+ * max of the high words, max of the low words among those, min of the indices
+ * among those -- three instructions instead of five rounds of four shuffles
+ * on the critical path of every cycle. Indices fit 32 bits (n <= 46340). */
 __device__ __forceinline__ void warp_best(double& v, long long& i)
 {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1)
+    const unsigned long long sign = 0x8000000000000000ULL;
+    const unsigned long long bits =
+            (unsigned long long) __double_as_longlong(v + 0.0); /* -0 -> +0 */
+    const unsigned long long key = i < 0 ? 0ULL :
+            (bits & sign) ? ~bits : (bits | sign);
+    const unsigned hi = (unsigned) (key >> 32), lo = (unsigned) key;
+    const unsigned mhi = __reduce_max_sync(0xffffffffu, hi);
+    const unsigned mlo = __reduce_max_sync(0xffffffffu, hi == mhi ? lo : 0u);
+    const bool winner = i >= 0 && hi == mhi && lo == mlo;
+    const unsigned midx = __reduce_min_sync(0xffffffffu,
+            winner ? (unsigned) i : 0xffffffffu);
+    if (midx == 0xffffffffu)
     {
-        const double ov = __shfl_xor_sync(0xffffffffu, v, o);
-        const long long oi = __shfl_xor_sync(0xffffffffu, i, o);
-        if (beats(ov, oi, v, i)) { v = ov; i = oi; }
+        v = 0.0;
+        i = -1;
+        return;
     }
+    const unsigned long long best = ((unsigned long long) mhi << 32) | mlo;
+    v = __longlong_as_double((long long) ((best & sign) ? (best & ~sign) : ~best));
+    i = (long long) midx;
 }
 
 struct Header
