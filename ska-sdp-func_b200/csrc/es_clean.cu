@@ -32,6 +32,7 @@
  * beam sample (cbeam_dim / 2 - 1 - ...) under the component, sdp_fft_convolution
  * .cpp:127-244) is kept: see beam_offset().
  */
+#include <math.h>
 #include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
@@ -156,22 +157,30 @@ __global__ void __launch_bounds__(ES_CLEAN_THREADS) es_hogbom_cycles_kernel(
     T* res = IN_SMEM ? reinterpret_cast<T*>(s_raw) : residual + lo;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 
+    /* Per-element work is kept to a handful of instructions (the kernel is
+     * bound by instruction issue: ncu counted 715 warp instructions per cycle
+     * and warp for 8 elements per thread before this form): 32-bit local
+     * indices, the running peak in the image type with a strict `>` (a thread
+     * visits its elements in rising index order, so the first of equal maxima
+     * stays), (row, column) advanced by a fixed step. */
+    const int ni = (int) n;
+    const int mine32 = (int) mine;
+    const T lowest = -(T) INFINITY;
+    T bestv = lowest;
+    int bestk = -1;
     /* first pass: load the slice, find its peak */
-    double best = 0.0;
-    long long best_idx = -1;
-    for (int64_t k = threadIdx.x; k < mine; k += ES_CLEAN_THREADS)
+    for (int k = threadIdx.x; k < mine32; k += ES_CLEAN_THREADS)
     {
         const T r = residual[lo + k];
         if (IN_SMEM) res[k] = r;
-        if (beats((double) r, lo + k, best, best_idx))
-        {
-            best = (double) r;
-            best_idx = lo + k;
-        }
+        if (r > bestv) { bestv = r; bestk = k; }
     }
+    double best = (double) bestv;
+    long long best_idx = bestk < 0 ? -1 : lo + bestk;
 
-    const int64_t first_i = (lo + threadIdx.x) / n;
-    const int64_t first_j = (lo + threadIdx.x) - first_i * n;
+    const int first_i = (int) ((lo + threadIdx.x) / n);
+    const int first_j = (int) ((lo + threadIdx.x) - (int64_t) first_i * n);
+    const int step_i = ES_CLEAN_THREADS / ni, step_j = ES_CLEAN_THREADS % ni;
     int cycle = 0, num_components = 0;
     for (;; ++cycle)
     {
@@ -258,15 +267,14 @@ __global__ void __launch_bounds__(ES_CLEAN_THREADS) es_hogbom_cycles_kernel(
         T before = (T) 0;
         if (writer) before = __ldcg(clean_model + peak_idx);
         /* subtract the shifted PSF from the slice, look for the next peak */
-        const int64_t mx = peak_idx / n, my = peak_idx - mx * n;
-        const T* window = psf + (n - mx) * 2 * n + (n - my);
-        best = 0.0;
-        best_idx = -1;
-        /* (i, j) of the thread's elements advance by ES_CLEAN_THREADS columns:
-         * one division per cycle instead of one per element */
-        int64_t i = first_i, j = first_j;
-        for (int64_t k0 = threadIdx.x; k0 < mine;
-                k0 += (int64_t) ES_CLEAN_UNROLL * ES_CLEAN_THREADS)
+        const int mx = (int) ((unsigned) peak_idx / (unsigned) ni);
+        const int my = (int) peak_idx - mx * ni;
+        const T* window = psf + ((int64_t) (ni - mx) * 2 * ni + (ni - my));
+        bestv = lowest;
+        bestk = -1;
+        int i = first_i, j = first_j;
+        for (int k0 = threadIdx.x; k0 < mine32;
+                k0 += ES_CLEAN_UNROLL * ES_CLEAN_THREADS)
         {
             /* all PSF loads of the group in flight before the first use (an
              * L2 round trip each: one at a time they are the whole cycle) */
@@ -275,25 +283,24 @@ __global__ void __launch_bounds__(ES_CLEAN_THREADS) es_hogbom_cycles_kernel(
             for (int u = 0; u < ES_CLEAN_UNROLL; ++u)
             {
                 p[u] = (T) 0;
-                if (k0 + (int64_t) u * ES_CLEAN_THREADS < mine)
-                    p[u] = window[i * 2 * n + j];
-                j += ES_CLEAN_THREADS;
-                while (j >= n) { j -= n; ++i; }
+                if (k0 + u * ES_CLEAN_THREADS < mine32)
+                    p[u] = window[(int64_t) i * (2 * ni) + j];
+                i += step_i;
+                j += step_j;
+                if (j >= ni) { j -= ni; ++i; }
             }
 #pragma unroll
             for (int u = 0; u < ES_CLEAN_UNROLL; ++u)
             {
-                const int64_t k = k0 + (int64_t) u * ES_CLEAN_THREADS;
-                if (k >= mine) break;
+                const int k = k0 + u * ES_CLEAN_THREADS;
+                if (k >= mine32) break;
                 const T r = subtract<T>(res[k], gain, peak, p[u]);
                 res[k] = r;
-                if (beats((double) r, lo + k, best, best_idx))
-                {
-                    best = (double) r;
-                    best_idx = lo + k;
-                }
+                if (r > bestv) { bestv = r; bestk = k; }
             }
         }
+        best = (double) bestv;
+        best_idx = bestk < 0 ? -1 : lo + bestk;
         if (writer)
         {
             if (before == (T) 0) components[num_components++] = (int) peak_idx;
@@ -303,7 +310,7 @@ __global__ void __launch_bounds__(ES_CLEAN_THREADS) es_hogbom_cycles_kernel(
         __syncthreads();
     }
     if (IN_SMEM)
-        for (int64_t k = threadIdx.x; k < mine; k += ES_CLEAN_THREADS)
+        for (int k = threadIdx.x; k < mine32; k += ES_CLEAN_THREADS)
             residual[lo + k] = res[k];
     /* nobody may still be reading this CTA's candidates when it exits */
     if (MODE == ES_CLEAN_CLUSTER) cg::this_cluster().sync();
