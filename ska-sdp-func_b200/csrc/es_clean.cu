@@ -418,6 +418,9 @@ int run(const int64_t n, const T* psf, const double loop_gain,
     /* small images: ONE cluster of 16 (or 8) CTAs holds the whole residual in
      * its shared memory and exchanges the candidates through it */
     const char* no_cluster = getenv("SKA_SDP_FUNC_CLEAN_NO_CLUSTER");
+    int max_groups = 1; /* groups of PSF loads per thread and cycle */
+    if (const char* e = getenv("SKA_SDP_FUNC_CLEAN_CLUSTER_GROUPS"))
+        if (atoi(e) > 0) max_groups = atoi(e);
     for (int csize = 16; csize >= 8 && !launched &&
             !(no_cluster && atoi(no_cluster) > 0); csize /= 2)
     {
@@ -428,7 +431,8 @@ int run(const int64_t n, const T* psf, const double loop_gain,
          * cycle (measured: 256^2 4.2 vs 5.0 us per cycle, 512^2 8.7 vs 5.0) */
         if (slice_bytes + 2048 > (size_t) smem_max ||
                 total < (int64_t) csize * ES_CLEAN_THREADS ||
-                slice > (int64_t) ES_CLEAN_UNROLL * ES_CLEAN_THREADS) continue;
+                slice > (int64_t) max_groups * ES_CLEAN_UNROLL * ES_CLEAN_THREADS)
+            continue;
         const void* fn = (const void*) es_hogbom_cycles_kernel<T, ES_CLEAN_CLUSTER>;
         if (cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize,
                 (int) slice_bytes) != cudaSuccess ||
