@@ -373,6 +373,14 @@ __global__ void __launch_bounds__(256) es_clean_restore_kernel(const int64_t n,
 
 size_t align256(const size_t b) { return (b + 255) & ~(size_t) 255; }
 
+/* entries of the component list: one per cycle, and never more than pixels */
+size_t list_entries(const int64_t n, const int cycle_limit)
+{
+    const int64_t cycles = cycle_limit > 0 ? cycle_limit : 1;
+    return (size_t) (cycles < n * n ? cycles : n * n);
+}
+
+
 /* Beam sample under a component: the reference pads both images to P (power
  * of two >= n + dim - 1) at (P - size) / 2, multiplies the spectra, shifts by
  * P / 2 and crops from (P - n) / 2 - 1 (sdp_fft_convolution.cpp:127-244):
@@ -395,7 +403,8 @@ int run(const int64_t n, const T* psf, const double loop_gain,
     Cand* cand = (Cand*) (scratch + 256);
     int* components = (int*) (scratch + 256 +
             align256(2 * ES_CLEAN_MAX_CTAS * sizeof(Cand)));
-    T* cbeam = (T*) ((char*) components + align256((size_t) cycle_limit * 4));
+    T* cbeam = (T*) ((char*) components +
+            align256(list_entries(n, cycle_limit) * 4));
 
     int dev = 0, sms = 0, coop = 0, smem_max = 0;
     cudaError_t err = cudaGetDevice(&dev);
@@ -434,8 +443,11 @@ int run(const int64_t n, const T* psf, const double loop_gain,
                 slice > (int64_t) max_groups * ES_CLEAN_UNROLL * ES_CLEAN_THREADS)
             continue;
         const void* fn = (const void*) es_hogbom_cycles_kernel<T, ES_CLEAN_CLUSTER>;
+        /* the opt-in belongs to the function and the device, not to a call:
+         * always the device maximum, so that concurrent calls with other
+         * slice sizes cannot lower it under each other */
         if (cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                (int) slice_bytes) != cudaSuccess ||
+                smem_max - 2048) != cudaSuccess ||
                 (csize > 8 && cudaFuncSetAttribute(fn,
                 cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess))
         {
@@ -497,7 +509,7 @@ int run(const int64_t n, const T* psf, const double loop_gain,
         {
             err = cudaFuncSetAttribute(fn,
                     cudaFuncAttributeMaxDynamicSharedMemorySize,
-                    (int) slice_bytes);
+                    smem_max - 2048);
             if (err != cudaSuccess) return (int) err;
         }
         int per_sm = 0;
@@ -527,11 +539,11 @@ int run(const int64_t n, const T* psf, const double loop_gain,
 
 extern "C" {
 
-size_t es_hogbom_scratch_bytes(int cycle_limit, int64_t cbeam_dim,
+size_t es_hogbom_scratch_bytes(int64_t n, int cycle_limit, int64_t cbeam_dim,
         int is_double)
 {
     return 256 + align256(2 * ES_CLEAN_MAX_CTAS * sizeof(Cand)) +
-            align256((size_t) (cycle_limit > 0 ? cycle_limit : 1) * 4) +
+            align256(list_entries(n, cycle_limit) * 4) +
             align256((size_t) (cbeam_dim > 0 ? cbeam_dim * cbeam_dim : 1) *
                     (is_double ? 8 : 4));
 }

@@ -12,9 +12,10 @@
 extern "C" {
 #endif
 
-/* Bytes of device scratch es_hogbom_clean needs for `cycle_limit` cycles and a
- * cbeam_dim x cbeam_dim CLEAN beam (is_double: element type of the images). */
-size_t es_hogbom_scratch_bytes(int cycle_limit, int64_t cbeam_dim,
+/* Bytes of device scratch es_hogbom_clean needs for n x n images,
+ * `cycle_limit` cycles and a cbeam_dim x cbeam_dim CLEAN beam (is_double:
+ * element type of the images). */
+size_t es_hogbom_scratch_bytes(int64_t n, int cycle_limit, int64_t cbeam_dim,
         int is_double);
 
 /* The whole minor cycle and the restore step (sdp_hogbom_clean.cpp:113-277):

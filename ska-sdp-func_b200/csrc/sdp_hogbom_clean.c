@@ -145,7 +145,7 @@ void sdp_hogbom_clean(const sdp_Mem* dirty_img, const sdp_Mem* psf,
     const int on_host = (location != SDP_MEM_GPU);
     const int is_double = (type == SDP_MEM_DOUBLE);
     const size_t image_bytes = (size_t) (n * n) * (is_double ? 8 : 4);
-    const size_t scratch_bytes = es_hogbom_scratch_bytes(cycle_limit,
+    const size_t scratch_bytes = es_hogbom_scratch_bytes(n, cycle_limit,
             cbeam_dim, is_double);
     char* block = 0;
     cudaError_t err = cudaMalloc((void**) &block, scratch_bytes +
